@@ -1,0 +1,267 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (imported from
+/root/reference through oracle/ref_harness.py) on seeded synthetic inputs.
+
+Run in the build container only:   python oracle/gen_golden.py
+The fixtures are committed; the GPU box never needs /root/reference.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, HERE)
+sys.path.insert(0, ROOT)
+
+import ref_harness  # noqa: E402
+from romtime_b200 import synthetic  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def tridiag_topology(n):
+    rows, cols = [], []
+    for i in range(n):
+        for j in (i - 1, i, i + 1):
+            if 0 <= j < n:
+                rows.append(i)
+                cols.append(j)
+    return np.array(rows), np.array(cols)
+
+
+def gen_orth():
+    from romtime.rom.pod import orth
+
+    rng = np.random.default_rng(11)
+    out = {}
+    cases = []
+    # (name, matrix, kwargs)
+    A = rng.standard_normal((300, 24)) @ np.diag(10.0 ** (-np.arange(24) / 4.0)) @ rng.standard_normal((24, 24))
+    cases.append(("graded_num", A, dict(num=6)))
+    cases.append(("graded_tol", A, dict(tol=1.0 - 1e-6)))
+    cases.append(("graded_default", A, dict()))
+    cases.append(("graded_nonorm", A, dict(num=5, normalize=False)))
+    cases.append(("graded_vt", np.asfortranarray(A), dict(num=4, return_VT=True)))
+    B = synthetic.pod_snapshots(2000, 64, seed=1003, modes=24, decay=4.0, noise=0.0)
+    cases.append(("c3like_C", B, dict(num=8)))
+    cases.append(("c3like_F", np.asfortranarray(B), dict(num=8)))
+    Cm = synthetic.mdeim_snapshots(600, 40, seed=1004)
+    cases.append(("c4like", Cm, dict(num=10, normalize=False)))
+    lowrank = rng.standard_normal((150, 5)) @ rng.standard_normal((5, 30))
+    cases.append(("lowrank_default", lowrank, dict()))
+    cases.append(("wide_tol", rng.standard_normal((40, 12)), dict(tol=0.9)))
+    names = []
+    for name, M, kw in cases:
+        res = orth(M, **kw)
+        names.append(name)
+        out[f"{name}/S"] = M
+        out[f"{name}/order"] = np.array("F" if M.flags.f_contiguous and not M.flags.c_contiguous else "C")
+        out[f"{name}/kw"] = np.array(repr(kw))
+        out[f"{name}/Q"] = res[0]
+        out[f"{name}/s"] = res[1]
+        out[f"{name}/energy"] = res[2]
+        if len(res) == 4:
+            out[f"{name}/VT"] = res[3]
+    out["names"] = np.array(names)
+    np.savez_compressed(os.path.join(GOLD, "orth.npz"), **out)
+    print("orth:", names)
+
+
+def gen_greedy():
+    from romtime.deim.deim import DiscreteEmpiricalInterpolation
+    from romtime.rom.pod import orth
+
+    rng = np.random.default_rng(12)
+    out, names = {}, []
+
+    def run(name, basis):
+        d = DiscreteEmpiricalInterpolation(assemble=None, name=name)
+        d.basis_fom = basis
+        dofs, P = d.build_interpolation_mesh()
+        out[f"{name}/basis"] = basis
+        out[f"{name}/dofs"] = np.array(dofs, dtype=np.int64)
+        out[f"{name}/PT_U"] = np.matmul(P.T, basis)
+        names.append(name)
+
+    Q, _, _ = orth(rng.standard_normal((500, 40)), num=12)
+    run("random_orth", np.ascontiguousarray(Q))
+    run("random_orth_F", np.asfortranarray(Q))
+    # MDEIM-like basis with bit-identical duplicated rows (symmetric off-diagonals)
+    S = synthetic.mdeim_snapshots(900, 60, seed=1004)
+    Qm, _, _ = orth(S, num=16, normalize=False)
+    run("mdeim_dup", Qm)
+    # raw (non-orthogonal) basis, single column, and exact ties in column 0
+    run("raw", rng.standard_normal((257, 9)))
+    run("single", rng.standard_normal((33, 1)))
+    tie = rng.standard_normal((64, 5))
+    tie[10, :] = tie[3, :]
+    tie[3, 0] = tie[10, 0] = 9.0
+    run("ties", tie)
+    out["names"] = np.array(names)
+    np.savez_compressed(os.path.join(GOLD, "greedy.npz"), **out)
+    print("greedy:", {n: out[f"{n}/dofs"][:6].tolist() for n in names})
+
+
+def gen_project_interp():
+    from romtime.deim.deim import DiscreteEmpiricalInterpolation
+    from romtime.deim.mdeim import MatrixDiscreteEmpiricalInterpolation
+
+    rng = np.random.default_rng(13)
+    Nh, N, m = 120, 7, 9
+    V, _ = np.linalg.qr(rng.standard_normal((Nh, N)))
+    out = {"V": V}
+    # DEIM (vector)
+    Uf, _ = np.linalg.qr(rng.standard_normal((Nh, m)))
+    coefs = rng.standard_normal((m, 4))
+
+    def assemble_vec(mu, t, entries=None):
+        full = Uf @ (coefs @ np.array([1.0, mu["a"], t, mu["a"] * t]))
+        if entries is None:
+            return full
+        return np.array([full[e[0]] for e in entries])
+
+    d = DiscreteEmpiricalInterpolation(assemble=assemble_vec, name="vec")
+    d.basis_fom = Uf
+    dofs, P = d.build_interpolation_mesh()
+    d.store_dofs(dofs)
+    d.PT_U = np.matmul(P.T, Uf)
+    d.project_basis(V)
+    mu, t = {"a": 0.7}, 0.3
+    out["deim/basis_fom"] = Uf
+    out["deim/dofs"] = np.array(dofs, dtype=np.int64)
+    out["deim/PT_U"] = d.PT_U
+    out["deim/basis_rom"] = d.basis_rom
+    out["deim/f_local"] = assemble_vec(mu, t, d.dofs)
+    out["deim/thetas"] = d.compute_thetas(out["deim/f_local"])
+    out["deim/interp_fom"] = d.interpolate(mu, t, which="fom")
+    out["deim/interp_rom"] = d.interpolate(mu, t, which="rom")
+    # MDEIM (matrix): tridiagonal topology
+    rows, cols = tridiag_topology(Nh)
+    nnz = len(rows)
+    Um, _ = np.linalg.qr(rng.standard_normal((nnz, m)))
+    Um[0, :] = 0.0  # reference zeroes snapshot row 0 (deim/deim.py:388-389)
+
+    def assemble_mat(mu, t, entries=None):
+        full = Um @ (coefs @ np.array([1.0, mu["a"], t, mu["a"] * t]))
+        look = {(int(r), int(c)): k for k, (r, c) in enumerate(zip(rows, cols))}
+        return np.array([full[look[(int(e[0]), int(e[1]))]] for e in entries])
+
+    md = MatrixDiscreteEmpiricalInterpolation(assemble=assemble_mat, name="mat")
+    md.basis_fom = Um
+    md.rows, md.cols = rows, cols
+    dofs, P = md.build_interpolation_mesh()
+    md.store_dofs(dofs)
+    md.PT_U = np.matmul(P.T, Um)
+    md.project_basis(V)
+    out["mdeim/basis_fom"] = Um
+    out["mdeim/rows"] = rows
+    out["mdeim/cols"] = cols
+    out["mdeim/dofs"] = np.array(dofs, dtype=np.int64)
+    out["mdeim/dofs_rc"] = np.array(md.dofs, dtype=np.int64)
+    out["mdeim/PT_U"] = md.PT_U
+    out["mdeim/basis_rom"] = md.basis_rom
+    out["mdeim/f_local"] = assemble_mat(mu, t, md.dofs)
+    out["mdeim/interp_rom"] = md.interpolate(mu, t, which="rom")
+    np.savez_compressed(os.path.join(GOLD, "project_interp.npz"), **out)
+    print("project/interp: deim dofs", dofs[:5], "basis_rom", md.basis_rom.shape)
+
+
+def build_reference_rom(model, V, bdf, dt, nt, direct):
+    """Wire a reference RomConstructorNonlinear to the synthetic model."""
+    from romtime.deim.deim import DiscreteEmpiricalInterpolation
+    from romtime.deim.mdeim import MatrixDiscreteEmpiricalInterpolation
+    from romtime.deim.nonlinear import MatrixDiscreteEmpiricalInterpolationNonlinear
+    from romtime.rom.rom import RomConstructorNonlinear
+    import romtime_oracle as orc
+
+    N, m = model["N"], model["m"]
+    fom = ref_harness.DuckFom(Nh=V.shape[0], dt=dt, nt=nt, bdf_scheme=bdf)
+    rom = RomConstructorNonlinear(fom=fom, grid=None, name="golden")
+    rom.setup(rnd=0)
+    rom.basis = V
+    if direct:
+        rom.algebraic_solver = lambda A, b: (np.linalg.solve(A, b), 0)
+    Tfom = model["trilinear"]["T"] @ V.T  # (m, Nh): Tfom @ (V u) == T u
+
+    def feats(mu, t):
+        return orc.piston_features(mu["a0"], mu["omega"], mu["delta"], t, model["which"])
+
+    def make(op):
+        C = model[op]["C"]
+        if op == "trilinear":
+            def assemble(mu, t, entries=None, u_n=None):
+                phi = feats(mu, t)
+                return C @ phi + phi[11] * (Tfom @ u_n)
+            r = MatrixDiscreteEmpiricalInterpolationNonlinear(assemble=assemble, name=op)
+        elif op == "rhs":
+            def assemble(mu, t, entries=None):
+                return C @ feats(mu, t)
+            r = DiscreteEmpiricalInterpolation(assemble=assemble, name=op)
+        else:
+            def assemble(mu, t, entries=None):
+                return C @ feats(mu, t)
+            r = MatrixDiscreteEmpiricalInterpolation(assemble=assemble, name=op)
+        mm = model[op]["PT_U"].shape[0]
+        r.basis_fom = np.zeros((1, mm))  # only .shape[1] is read online (deim/deim.py:106-108)
+        r.basis_rom = model[op]["basis_rom"]
+        r.PT_U = model[op]["PT_U"]
+        r.dofs = [(k,) for k in range(mm)]
+        r.N_V = N
+        return r
+
+    rom.mdeim_Mh = make("mass")
+    rom.mdeim_Ah = make("stiffness")
+    rom.mdeim_Ch = make("convection")
+    rom.mdeim_Nh = make("trilinear")
+    rom.mdeim_Nh_hat = make("nonlinear_lifting")
+    rom.deim_fgh = make("rhs")
+    return rom
+
+
+def gen_solve():
+    rng = np.random.default_rng(14)
+    out, names = {}, []
+    for name, kw in (
+        ("n8m6", dict(N=8, m=6, seed=21)),
+        ("n16m10_pivot", dict(N=16, m=10, m_rhs=7, seed=22, mass_identity=0.15, coupling=1.0)),
+    ):
+        model = synthetic.make_piston_model(**kw)
+        N = model["N"]
+        V, _ = np.linalg.qr(rng.standard_normal((40, N)))
+        mus = synthetic.sample_mus(3, seed=kw["seed"])
+        dt, nt = 1e-3, 25
+        out[f"{name}/kw"] = np.array(repr(kw))
+        out[f"{name}/mus"] = mus
+        out[f"{name}/dt"] = np.array(dt)
+        out[f"{name}/nt"] = np.array(nt)
+        for op in synthetic.OPS:
+            for key in ("basis_rom", "PT_U", "C", "T"):
+                val = model[op][key]
+                if val is not None:
+                    out[f"{name}/{op}/{key}"] = val
+        for bdf in ("1", "2"):
+            for direct in (True, False):
+                sols = []
+                for mu_row in mus:
+                    rom = build_reference_rom(model, V, bdf, dt, nt, direct)
+                    mu = {"a0": mu_row[0], "omega": mu_row[1], "delta": mu_row[2]}
+                    rom.solve(mu=mu, step="online")
+                    sols.append(np.array(rom.solutions.rom))
+                tag = f"{name}/bdf{bdf}_{'direct' if direct else 'gmres'}"
+                out[tag] = np.stack(sols)  # (B, N, nt)
+        names.append(name)
+    out["names"] = np.array(names)
+    np.savez_compressed(os.path.join(GOLD, "solve.npz"), **out)
+    print("solve:", names, {k: v.shape for k, v in out.items() if "bdf" in k})
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLD, exist_ok=True)
+    ref_harness.load_reference()
+    gen_orth()
+    gen_greedy()
+    gen_project_interp()
+    gen_solve()
+    for f in sorted(os.listdir(GOLD)):
+        print(f, os.path.getsize(os.path.join(GOLD, f)))
