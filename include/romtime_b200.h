@@ -1,0 +1,180 @@
+/* romtime_b200.h -- C ABI of libromtime_b200.so (B200 / sm_100a).
+ *
+ * Drop-in boundary for the offline-compression + online-solve hot path of KikeM/romtime
+ * (reference @ 7bca28a; file:line citations are relative to the reference's src/romtime/).
+ * The reference has no FFI layer: its boundary is the Python API, and the arithmetic goes to
+ * LAPACK/BLAS through NumPy/SciPy.  Every entry point below replaces one of those call sites;
+ * the Python classes in romtime_b200/ (same names and signatures as the reference) call them
+ * through ctypes (see INTEGRATION.md for the reference-side stubs).
+ *
+ * Conventions
+ *  - plain C: pointers + sizes, no torch types.  Every function returns an rt_status
+ *    (0 = ok, negative = error); nothing throws across the ABI.  rt_last_error(h) gives text.
+ *  - all matrix/vector pointers are DEVICE pointers owned by the caller (allocated by torch and
+ *    handed over as data_ptr()); the library never frees or keeps them.  Scratch memory is owned
+ *    by the handle.  `stream` is a cudaStream_t passed as void* (0 = legacy default stream); all
+ *    work is enqueued on it and the call returns without synchronising unless stated.
+ *  - matrices are fp64 with explicit element strides (stride_row, stride_col) so that NumPy
+ *    C-order (np.hstack, rom/rom.py:368) and F-order (np.array(list).T, deim/deim.py:384;
+ *    LAPACK outputs) arrays are both accepted without a host-side copy.
+ *  - indices are int64 (NumPy intp).
+ *  - one handle per device; a handle is not thread-safe.
+ */
+#ifndef ROMTIME_B200_H
+#define ROMTIME_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_handle rt_handle;
+
+typedef enum {
+    RT_OK = 0,
+    RT_EINVAL = -1,    /* bad argument (null pointer, negative size, unsupported shape)          */
+    RT_ECUDA = -2,     /* CUDA runtime / driver error; text in rt_last_error                     */
+    RT_ESINGULAR = -3, /* exactly singular matrix (mirrors numpy.linalg.LinAlgError)             */
+    RT_ENOMEM = -4,    /* scratch allocation failed                                              */
+    RT_ENOTCONV = -5,  /* eigensolver did not converge within its sweep limit                    */
+    RT_ENODEVICE = -6  /* no sm_100 device: there is NO CPU fallback                             */
+} rt_status;
+
+#define RT_NF 12     /* number of (mu, t) features of the piston evaluator, see rt_rom_model */
+#define RT_MAX_OPS 8
+
+/* ---------------------------------------------------------------- life cycle -------- */
+int rt_version(void);
+int rt_create(int device, rt_handle** out);
+int rt_destroy(rt_handle* h);
+const char* rt_last_error(const rt_handle* h);
+/* measured FP64 DMMA peak of this device in TFLOP/s (register-resident mma.sync.m8n8k4.f64 loop);
+ * synchronous.  Used as the roofline denominator of the FP64-bound kernels. */
+int rt_fp64_peak_tflops(rt_handle* h, double* tflops);
+
+/* ---------------------------------------------------------------- POD (rom/pod.py:7-62) */
+/* Snapshot Gram matrix  G = S^T S  (n x n, symmetric, written in full, row-major == col-major)
+ * and column norms  colnorm[j] = sqrt(G[j][j])  (rom/pod.py:32-33 computes np.linalg.norm(axis=0)).
+ * normalize != 0: G <- D^-1 G D^-1 with D = diag(colnorm), i.e. the Gram matrix of the
+ * column-normalised snapshots that rom/pod.py:33 feeds to gesvd (:38).
+ * Rows [row0, row0+rows) only are read when rows < Nh is wanted: pass the sub-pointer. */
+int rt_pod_gram_f64(rt_handle* h, const double* S, int64_t Nh, int64_t n, int64_t stride_row,
+                    int64_t stride_col, int normalize, double* G, double* colnorm, void* stream);
+
+/* Cross Gram block  C = A^T B  (na x nb), A: Nh x na, B: Nh x nb, C row-major with leading
+ * dimension ldc.  Used for the column-sharded multi-GPU Gram (block row G[g,:] = S_g^T [S_0 .. S_P-1],
+ * followed by an NCCL all-reduce of G issued by the host) and for DEIM.project_basis
+ * (V^T U_f, deim/deim.py:508-509). */
+int rt_gram_cross_f64(rt_handle* h, const double* A, int64_t na, int64_t a_stride_row,
+                      int64_t a_stride_col, const double* B, int64_t nb, int64_t b_stride_row,
+                      int64_t b_stride_col, int64_t Nh, double* C, int64_t ldc, void* stream);
+
+/* In-place finalisation of an assembled (e.g. all-reduced) Gram matrix: colnorm = sqrt(diag),
+ * optional D^-1 G D^-1 scaling, exact symmetrisation (lower <- upper). */
+int rt_gram_finalize_f64(rt_handle* h, double* G, int64_t n, int normalize, double* colnorm,
+                         void* stream);
+
+/* Symmetric eigen-decomposition  G = W diag(w) W^T  (replaces the right-singular side of
+ * scipy.linalg.svd(..., lapack_driver="gesvd"), rom/pod.py:38: s = sqrt(w), VT = W^T).
+ * G (n x n) is overwritten; W is written row-major n x n with eigenvector k in COLUMN k;
+ * w is sorted descending (gesvd ordering).  Parallel-order block Jacobi.  `info` (device int,
+ * may be NULL): number of sweeps used, or -1 if not converged. */
+int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int* info,
+                   void* stream);
+
+/* Basis lift  Q = S Wr  (Nh x r): left singular vectors from the Gram eigenvectors,
+ * Wr (n x r, row-major, leading dimension ldw) already scaled by 1/(sigma_k * colnorm_j).
+ * Q is written with strides (q_stride_row, q_stride_col). */
+int rt_pod_lift_f64(rt_handle* h, const double* S, int64_t Nh, int64_t n, int64_t stride_row,
+                    int64_t stride_col, const double* Wr, int64_t ldw, int64_t r, double* Q,
+                    int64_t q_stride_row, int64_t q_stride_col, void* stream);
+
+/* ---------------------------------------------- DEIM greedy (deim/deim.py:517-561) ---- */
+/* Classic DEIM point selection on the collateral basis U (Nh x m):
+ *   p_0 = argmax |u_0| ; c = (P^T U_j)^-1 P^T u_j ; res = u_j - U_j c ; p_j = argmax |res|
+ * with numpy.argmax semantics (FIRST maximum wins; NaN counts as maximum).
+ * Outputs (device): dofs[m] (int64), PT_U[m*m] row-major = U[dofs, :] (deim/deim.py:159, :212),
+ * info[1]: 0 ok, j>0 if the interpolation matrix became exactly singular at step j. */
+int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int64_t m, int64_t stride_row,
+                       int64_t stride_col, int64_t* dofs, double* PT_U, int* info, void* stream);
+
+/* ---------------------------------------------- projections ---------------------------- */
+/* DEIM.project_basis (deim/deim.py:495-515): out (N x m, row-major) = V^T U_f. */
+int rt_project_vec_f64(rt_handle* h, const double* V, int64_t v_stride_row, int64_t v_stride_col,
+                       const double* U, int64_t u_stride_row, int64_t u_stride_col, int64_t Nh,
+                       int64_t N, int64_t m, double* out, void* stream);
+
+/* MDEIM.project_basis (deim/mdeim.py:153-192 + utils.py:96-149): for every collateral mode q,
+ * A_q = csr(U[:, q]; rows, cols), out[(i*N + j), q] = (V^T A_q V)[i, j]; duplicates (rows[k],
+ * cols[k]) are summed like scipy's COO->CSR conversion.  out is (N*N) x m with element strides
+ * (out_stride_row, out_stride_col). */
+int rt_project_mat_f64(rt_handle* h, const double* U, int64_t u_stride_row, int64_t u_stride_col,
+                       const int64_t* rows, const int64_t* cols, int64_t nnz, const double* V,
+                       int64_t v_stride_row, int64_t v_stride_col, int64_t Nh, int64_t N,
+                       int64_t m, double* out, int64_t out_stride_row, int64_t out_stride_col,
+                       void* stream);
+
+/* ---------------------------------------------- theta solve + assembly ----------------- */
+/* Inverse of a small dense matrix by Gauss-Jordan with partial pivoting ("factor once",
+ * replaces the per-call LU of np.linalg.solve, deim/deim.py:491-492).  A, Ainv: m x m row-major.
+ * info (device int): 0 ok, k>0 zero pivot at step k. */
+int rt_invert_f64(rt_handle* h, const double* A, int64_t m, double* Ainv, int* info, void* stream);
+
+/* compute_thetas for a batch (deim/deim.py:477-493): theta[b, :] = PT_U^-1 F[b, :].
+ * PT_Uinv from rt_invert_f64; F, theta: B x m row-major. */
+int rt_theta_f64(rt_handle* h, const double* PT_Uinv, int64_t m, const double* F, int64_t B,
+                 double* theta, void* stream);
+
+/* _interpolate for a batch (deim/deim.py:445): out[b, :] = sum_q theta[b, q] * basis[:, q].
+ * basis: R x m with element strides; out: B x R row-major (R = N*N for MDEIM which="rom",
+ * reshaped (N, N) row-major per deim/mdeim.py:250-251). */
+int rt_assemble_batch_f64(rt_handle* h, const double* basis, int64_t R, int64_t m,
+                          int64_t b_stride_row, int64_t b_stride_col, const double* theta,
+                          int64_t B, double* out, void* stream);
+
+/* ---------------------------------------------- online sweep (rom/rom.py:430-555) ------ */
+/* One hyper-reduced operator of the ROM (a DEIM/MDEIM/N-MDEIM reductor after project_basis). */
+typedef struct {
+    int32_t m;               /* collateral basis size (deim N)                                     */
+    int32_t is_vector;       /* 0: matrix operator (basis_rom is N*N x m), 1: vector (N x m)       */
+    const double* basis_rom; /* column q contiguous: element (r, q) at basis_rom[q * ld + r]       */
+    int64_t ld;              /* leading dimension of basis_rom (>= N*N or N)                       */
+    const double* PT_Uinv;   /* m x m row-major, from rt_invert_f64                                */
+    const double* C;         /* m x RT_NF row-major: sampled entries f = C phi(mu,t) (+ b0 T u*)   */
+    const double* T;         /* m x N row-major or NULL: state-dependent part (trilinear operator) */
+} rt_rom_operator;
+
+/* RomConstructorNonlinear model (rom/rom.py:877-929).  ops order: mass, stiffness, convection,
+ * nonlinear_lifting, trilinear, rhs.  evaluator: 0 = piston "rest", 1 = piston "sudden"
+ * (problems/piston.py:18-60). */
+typedef struct {
+    int32_t N;
+    int32_t n_ops; /* 6 */
+    int32_t evaluator;
+    int32_t reserved;
+    rt_rom_operator ops[RT_MAX_OPS];
+} rt_rom_model;
+
+/* Batched RomConstructorNonlinear.solve: for every parameter b (mu[b, 0:3] = a0, omega, delta)
+ * run nt implicit BDF steps from a zero initial condition (rom/rom.py:451-452):
+ *   sampled entries -> theta -> K = bdf M + dt (A + C + N(u*) + N^) -> b = M w + dt f -> K u = b
+ * (dense LU with partial pivoting replaces GMRES, rom/rom.py:36, :492).
+ * bdf: 1 or 2.  uN_out: B x nt x N (row-major; [b][n][:] = reduced solution after step n).
+ * info: B ints, 0 ok, n>0 zero pivot at step n.  All pointers device. */
+int rt_online_sweep_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B,
+                        int64_t nt, double dt, int bdf, double* uN_out, int* info, void* stream);
+
+/* Same sweep that only keeps the final state (uN_last: B x N) -- used for long benchmark sweeps
+ * where the B x nt x N history (33.5 GB at C5) is not wanted on the device. */
+int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B,
+                             int64_t nt, double dt, int bdf, double* uN_last, int* info,
+                             void* stream);
+
+/* number of kernels launched by this handle since creation (bench.py "gpu_launches") */
+int64_t rt_launch_count(const rt_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROMTIME_B200_H */

@@ -1,0 +1,76 @@
+"""Thin functional wrappers over the C ABI (include/romtime_b200.h).
+
+Inputs may be NumPy arrays (copied to the current CUDA device through pinned staging by torch)
+or CUDA torch tensors (used in place, any 2-D strides).  Outputs are CUDA torch tensors; the
+reference-facing classes in romtime_b200/rom and romtime_b200/deim convert them to NumPy.
+Nothing here computes on the CPU: without the shared object or a GPU every call raises.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import c_vp, check, handle, load_library, stream_ptr
+
+F64 = torch.float64
+
+
+def to_device(a, dtype=F64):
+    """NumPy / torch (any device) -> CUDA tensor, strides preserved (C- and F-order both kept)."""
+    if isinstance(a, torch.Tensor):
+        t = a
+    else:
+        arr = np.asarray(a)
+        if arr.dtype != (np.float64 if dtype == F64 else np.int64):
+            arr = arr.astype(np.float64 if dtype == F64 else np.int64)
+        if not arr.flags.writeable:
+            arr = arr.copy(order="K")
+        t = torch.from_numpy(arr)
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    if not t.is_cuda:
+        t = t.to("cuda", non_blocking=False)
+    return t
+
+
+def _ptr(t):
+    return c_vp(t.data_ptr()) if t is not None else c_vp(0)
+
+
+def _strides2(t):
+    if t.dim() == 1:
+        return int(t.stride(0)), int(t.shape[0] * t.stride(0))
+    return int(t.stride(0)), int(t.stride(1))
+
+
+def fp64_peak_tflops():
+    out = ctypes.c_double(0.0)
+    h = handle()
+    check(load_library().rt_fp64_peak_tflops(h, ctypes.byref(out)), h, "rt_fp64_peak_tflops")
+    return out.value
+
+
+# ------------------------------------------------------------------ DEIM greedy
+def deim_greedy(U, sync=True):
+    """rt_deim_greedy_f64: returns (dofs int64[m], PT_U float64[m, m]) as CUDA tensors.
+
+    Raises numpy.linalg.LinAlgError when the interpolation matrix becomes exactly singular
+    (the reference raises it from np.linalg.solve, deim/deim.py:547)."""
+    Ud = to_device(U)
+    if Ud.dim() != 2:
+        raise ValueError("basis must be a 2-D array (Nh x m)")
+    Nh, m = Ud.shape
+    dofs = torch.empty(m, dtype=torch.int64, device=Ud.device)
+    PT_U = torch.empty((m, m), dtype=F64, device=Ud.device)
+    info = torch.zeros(1, dtype=torch.int32, device=Ud.device)
+    h = handle(Ud.device.index)
+    with torch.cuda.device(Ud.device):
+        rc = load_library().rt_deim_greedy_f64(h, _ptr(Ud), Nh, m, Ud.stride(0), Ud.stride(1),
+                                               _ptr(dofs), _ptr(PT_U), _ptr(info), stream_ptr())
+    check(rc, h, "rt_deim_greedy_f64")
+    if sync:
+        step = int(info.item())
+        if step != 0:
+            raise np.linalg.LinAlgError(f"Singular matrix (interpolation matrix singular after {step} points)")
+    return dofs, PT_U
