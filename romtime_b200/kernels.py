@@ -74,3 +74,63 @@ def deim_greedy(U, sync=True):
         if step != 0:
             raise np.linalg.LinAlgError(f"Singular matrix (interpolation matrix singular after {step} points)")
     return dofs, PT_U
+
+
+# ------------------------------------------------------------------ POD building blocks
+def pod_gram(S, normalize=True):
+    """rt_pod_gram_f64: (G n x n, colnorm n) for a snapshot matrix S (Nh x n), any 2-D strides."""
+    Sd = to_device(S)
+    Nh, n = Sd.shape
+    G = torch.empty((n, n), dtype=F64, device=Sd.device)
+    cn = torch.empty(n, dtype=F64, device=Sd.device)
+    h = handle(Sd.device.index)
+    with torch.cuda.device(Sd.device):
+        rc = load_library().rt_pod_gram_f64(h, _ptr(Sd), Nh, n, Sd.stride(0), Sd.stride(1), int(bool(normalize)),
+                                            _ptr(G), _ptr(cn), stream_ptr())
+    check(rc, h, "rt_pod_gram_f64")
+    return G, cn
+
+
+def gram_cross(A, B):
+    """rt_gram_cross_f64: C = A^T B (na x nb) for A (Nh x na), B (Nh x nb)."""
+    Ad, Bd = to_device(A), to_device(B)
+    Nh, na = Ad.shape
+    Nh2, nb = Bd.shape
+    if Nh != Nh2:
+        raise ValueError("row counts differ")
+    C = torch.empty((na, nb), dtype=F64, device=Ad.device)
+    h = handle(Ad.device.index)
+    with torch.cuda.device(Ad.device):
+        rc = load_library().rt_gram_cross_f64(h, _ptr(Ad), na, Ad.stride(0), Ad.stride(1), _ptr(Bd), nb,
+                                              Bd.stride(0), Bd.stride(1), Nh, _ptr(C), nb, stream_ptr())
+    check(rc, h, "rt_gram_cross_f64")
+    return C
+
+
+def gram_finalize(G, normalize=True):
+    n = G.shape[0]
+    cn = torch.empty(n, dtype=F64, device=G.device)
+    h = handle(G.device.index)
+    with torch.cuda.device(G.device):
+        rc = load_library().rt_gram_finalize_f64(h, _ptr(G), n, int(bool(normalize)), _ptr(cn), stream_ptr())
+    check(rc, h, "rt_gram_finalize_f64")
+    return cn
+
+
+def pod_lift(S, Wr, order="F"):
+    """rt_pod_lift_f64: Q = S @ Wr (Nh x r); Q is returned F-ordered (LAPACK-like) or C-ordered."""
+    Sd, Wd = to_device(S), to_device(Wr)
+    if not Wd.is_contiguous():
+        Wd = Wd.contiguous()
+    Nh, n = Sd.shape
+    r = Wd.shape[1]
+    if order == "F":
+        Q = torch.empty((r, Nh), dtype=F64, device=Sd.device).t()
+    else:
+        Q = torch.empty((Nh, r), dtype=F64, device=Sd.device)
+    h = handle(Sd.device.index)
+    with torch.cuda.device(Sd.device):
+        rc = load_library().rt_pod_lift_f64(h, _ptr(Sd), Nh, n, Sd.stride(0), Sd.stride(1), _ptr(Wd), Wd.stride(0), r,
+                                            _ptr(Q), Q.stride(0), Q.stride(1), stream_ptr())
+    check(rc, h, "rt_pod_lift_f64")
+    return Q
