@@ -1,0 +1,339 @@
+// Symmetric eigensolver for the POD Gram matrix: parallel-order BLOCK JACOBI in fp64.
+//
+// Replaces the right-singular side of scipy.linalg.svd(lapack_driver="gesvd") (rom/pod.py:38):
+// with G = S^T S,  s = sqrt(eig(G)),  VT = W^T.  Jacobi is used because it delivers all n
+// eigenpairs (orth returns the untruncated spectrum, rom/pod.py:59-62) with small relative errors
+// on graded positive semi-definite matrices, and maps to independent 64 x 64 tile problems:
+//
+//   blocks of 32 indices, round-robin tournament over block pairs (nb-1 rounds per sweep);
+//   per round  (1) k_jacobi_sub : one CTA per block pair diagonalises its 64 x 64 sub-matrix in
+//                                 shared memory (cyclic Jacobi, parallel ordering), keeps the
+//                                 accumulated rotation W_k;
+//              (2) k_jacobi_apply: A_kl <- W_k^T A_kl W_l for every tile pair k < l (DMMA, mirrored
+//                                 write keeps A exactly symmetric) and V[:, l] <- V[:, l] W_l.
+//   Converged when a whole sweep performs no rotation.  Rotation test: |a_pq| > eps*sqrt(|a_pp a_qq|).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BS = 32;        // block size
+constexpr int TS = 2 * BS;    // tile (sub-problem) size
+constexpr int LDS_ = TS + 4;  // shared-memory leading dimension (68 == 4 mod 16: conflict-free DMMA fragments)
+constexpr double kEps = 2.220446049250313e-16;
+
+__device__ __forceinline__ void rr_pair(int round, int k, int nb, int& I, int& J) {
+    // circle method on nb (even) players: every unordered pair meets exactly once in nb-1 rounds
+    const int m = nb - 1;
+    if (k == 0) { I = round % m; J = nb - 1; }
+    else { I = (round + k) % m; J = (round - k + m) % m; }
+    if (I > J) { int t = I; I = J; J = t; }
+}
+__device__ __forceinline__ int tile_index(int I, int J, int a) { return a < BS ? I * BS + a : J * BS + (a - BS); }
+
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+        : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__global__ void k_maxdiag(const double* __restrict__ A, int64_t n, int64_t lda, double* out) {
+    __shared__ double red[256];
+    double v = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) v = fmax(v, fabs(A[i * lda + i]));
+    red[threadIdx.x] = v;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) red[threadIdx.x] = fmax(red[threadIdx.x], red[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = red[0];
+}
+
+// ---- (1) 64 x 64 sub-problem: cyclic two-sided Jacobi with parallel ordering, in shared memory ----
+__global__ void __launch_bounds__(256) k_jacobi_sub(double* __restrict__ A, int64_t lda, int round, int nb,
+                                                    double* __restrict__ Wbuf, unsigned long long* rot_count,
+                                                    const double* __restrict__ maxdiag) {
+    constexpr int LD = TS + 1;
+    extern __shared__ __align__(16) double sub_sm[];
+    double* a = sub_sm;
+    double* w = sub_sm + TS * LD;
+    __shared__ double cs_c[BS], cs_s[BS];
+    __shared__ int pp[BS], qq[BS];
+    __shared__ int rotated;
+    __shared__ unsigned long long total;
+
+    const int tid = threadIdx.x;
+    int I, J;
+    rr_pair(round, blockIdx.x, nb, I, J);
+    for (int e = tid; e < TS * TS; e += 256) {
+        const int r = e / TS, c = e % TS;
+        a[r * LD + c] = A[(int64_t)tile_index(I, J, r) * lda + tile_index(I, J, c)];
+        w[r * LD + c] = (r == c) ? 1.0 : 0.0;
+    }
+    if (tid == 0) total = 0;
+    __syncthreads();
+    const double floor_abs = 1e-26 * maxdiag[0];
+
+    int prev_p = -1, prev_q = -1;
+    for (int sweep = 0; sweep < 40; ++sweep) {
+        if (tid == 0) rotated = 0;
+        __syncthreads();
+        for (int step = 0; step < TS - 1; ++step) {
+            if (tid < BS) {
+                if (prev_p >= 0) { a[prev_p * LD + prev_q] = 0.0; a[prev_q * LD + prev_p] = 0.0; }
+                int p, q;
+                rr_pair(step, tid, TS, p, q);
+                const double apq = a[p * LD + q], app = a[p * LD + p], aqq = a[q * LD + q];
+                double c = 1.0, s = 0.0;
+                const double mag = fabs(apq);
+                prev_p = -1;
+                if (mag > kEps * sqrt(fabs(app) * fabs(aqq)) && mag > floor_abs) {
+                    const double tau = (aqq - app) / (2.0 * apq);
+                    double t;
+                    if (fabs(tau) > 1e150) t = 0.5 / tau;
+                    else t = copysign(1.0, tau) / (fabs(tau) + sqrt(1.0 + tau * tau));
+                    c = rsqrt(1.0 + t * t);
+                    s = t * c;
+                    prev_p = p; prev_q = q;
+                    atomicAdd(&rotated, 1);
+                }
+                cs_c[tid] = c; cs_s[tid] = s; pp[tid] = p; qq[tid] = q;
+            }
+            __syncthreads();
+            // column rotation of A and W:  X[:, (p,q)] <- X[:, (p,q)] [c s; -s c]
+            for (int item = tid; item < BS * TS; item += 256) {
+                const int pr = item >> 6, i = item & (TS - 1);
+                const double c = cs_c[pr], s = cs_s[pr];
+                if (s != 0.0) {
+                    const int p = pp[pr], q = qq[pr];
+                    const double x = a[i * LD + p], y = a[i * LD + q];
+                    a[i * LD + p] = c * x - s * y;
+                    a[i * LD + q] = s * x + c * y;
+                    const double u = w[i * LD + p], v = w[i * LD + q];
+                    w[i * LD + p] = c * u - s * v;
+                    w[i * LD + q] = s * u + c * v;
+                }
+            }
+            __syncthreads();
+            // row rotation of A:  A[(p,q), :] <- [c -s; s c] A[(p,q), :]
+            for (int item = tid; item < BS * TS; item += 256) {
+                const int pr = item >> 6, j = item & (TS - 1);
+                const double c = cs_c[pr], s = cs_s[pr];
+                if (s != 0.0) {
+                    const int p = pp[pr], q = qq[pr];
+                    const double x = a[p * LD + j], y = a[q * LD + j];
+                    a[p * LD + j] = c * x - s * y;
+                    a[q * LD + j] = s * x + c * y;
+                }
+            }
+            __syncthreads();
+        }
+        if (tid == 0) total += (unsigned long long)rotated;
+        const int r = rotated;
+        __syncthreads();
+        if (r == 0) break;
+    }
+    if (tid < BS && prev_p >= 0) { a[prev_p * LD + prev_q] = 0.0; a[prev_q * LD + prev_p] = 0.0; }
+    __syncthreads();
+    for (int e = tid; e < TS * TS; e += 256) {
+        const int r = e / TS, c = e % TS;
+        A[(int64_t)tile_index(I, J, r) * lda + tile_index(I, J, c)] = a[r * LD + c];
+        Wbuf[(size_t)blockIdx.x * TS * TS + e] = w[r * LD + c];
+    }
+    if (tid == 0 && total) atomicAdd(rot_count, total);
+}
+
+// ---- (2) tile updates with DMMA:  A_kl <- W_k^T A_kl W_l  (k < l),  V_rl <- V_rl W_l ----
+// 8 warps, warp tile 16 x 32 of the 64 x 64 output.
+__device__ __forceinline__ void tile_gemm(const double* __restrict__ X, const double* __restrict__ Y, bool x_transposed,
+                                          int warp, int lane, double (&acc)[2][4][2]) {
+    // acc = op(X) * Y, op(X)[m][k] = x_transposed ? X[k][m] : X[m][k];  Y[k][n]
+    const int g = lane >> 2, tig = lane & 3;
+    const int m0 = (warp >> 1) * 16, n0 = (warp & 1) * 32;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+#pragma unroll 4
+    for (int k0 = 0; k0 < TS; k0 += 4) {
+        double af[2], bf[4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+            af[i] = x_transposed ? X[(k0 + tig) * LDS_ + m0 + 8 * i + g] : X[(m0 + 8 * i + g) * LDS_ + k0 + tig];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bf[j] = Y[(k0 + tig) * LDS_ + n0 + 8 * j + g];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_jacobi_apply(double* __restrict__ A, double* __restrict__ V, int64_t lda,
+                                                      int round, int nb, const double* __restrict__ Wbuf, int nA) {
+    extern __shared__ __align__(16) double sm[];
+    double* X = sm;
+    double* Wl = X + TS * LDS_;
+    double* Wk = Wl + TS * LDS_;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, tig = lane & 3;
+    const int m0 = (warp >> 1) * 16, n0 = (warp & 1) * 32;
+    const int P = nb / 2;
+    double acc[2][4][2];
+
+    if ((int)blockIdx.x < nA) {
+        // tile pair (k, l), k < l, from the linear index
+        int t = blockIdx.x, k = 0;
+        while (t >= P - 1 - k) { t -= P - 1 - k; ++k; }
+        const int l = k + 1 + t;
+        int Ik, Jk, Il, Jl;
+        rr_pair(round, k, nb, Ik, Jk);
+        rr_pair(round, l, nb, Il, Jl);
+        for (int e = tid; e < TS * TS; e += 256) {
+            const int r = e >> 6, c = e & 63;
+            X[r * LDS_ + c] = A[(int64_t)tile_index(Ik, Jk, r) * lda + tile_index(Il, Jl, c)];
+            Wl[r * LDS_ + c] = Wbuf[(size_t)l * TS * TS + e];
+            Wk[r * LDS_ + c] = Wbuf[(size_t)k * TS * TS + e];
+        }
+        __syncthreads();
+        tile_gemm(X, Wl, false, warp, lane, acc);  // T = X W_l
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                X[(m0 + 8 * i + g) * LDS_ + n0 + 8 * j + 2 * tig] = acc[i][j][0];
+                X[(m0 + 8 * i + g) * LDS_ + n0 + 8 * j + 2 * tig + 1] = acc[i][j][1];
+            }
+        __syncthreads();
+        tile_gemm(Wk, X, true, warp, lane, acc);  // A' = W_k^T T
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t gr = tile_index(Ik, Jk, m0 + 8 * i + g);
+                const int64_t gc = tile_index(Il, Jl, n0 + 8 * j + 2 * tig);  // gc, gc+1 are in the same block
+                A[gr * lda + gc] = acc[i][j][0];
+                A[gr * lda + gc + 1] = acc[i][j][1];
+                A[gc * lda + gr] = acc[i][j][0];
+                A[(gc + 1) * lda + gr] = acc[i][j][1];
+            }
+    } else {
+        const int t = blockIdx.x - nA;
+        const int l = t % P, rb = t / P;
+        int Il, Jl;
+        rr_pair(round, l, nb, Il, Jl);
+        for (int e = tid; e < TS * TS; e += 256) {
+            const int r = e >> 6, c = e & 63;
+            X[r * LDS_ + c] = V[((int64_t)rb * TS + r) * lda + tile_index(Il, Jl, c)];
+            Wl[r * LDS_ + c] = Wbuf[(size_t)l * TS * TS + e];
+        }
+        __syncthreads();
+        tile_gemm(X, Wl, false, warp, lane, acc);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t gr = (int64_t)rb * TS + m0 + 8 * i + g;
+                const int64_t gc = tile_index(Il, Jl, n0 + 8 * j + 2 * tig);
+                V[gr * lda + gc] = acc[i][j][0];
+                V[gr * lda + gc + 1] = acc[i][j][1];
+            }
+    }
+}
+
+__global__ void k_pad_copy(const double* __restrict__ G, int64_t n, double* __restrict__ A, double* __restrict__ V,
+                           int64_t npad) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= npad) return;
+    A[i * npad + j] = (i < n && j < n) ? G[i * n + j] : 0.0;
+    V[i * npad + j] = (i == j) ? 1.0 : 0.0;
+}
+
+// rank of each eigenvalue in descending order (ties by index), then scatter values and vectors
+__global__ void k_rank(const double* __restrict__ A, int64_t n, int64_t lda, int* __restrict__ rank, double* __restrict__ w) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double li = A[i * lda + i];
+    int r = 0;
+    for (int64_t j = 0; j < n; ++j) {
+        const double lj = A[j * lda + j];
+        r += (lj > li) || (lj == li && j < i);
+    }
+    rank[i] = r;
+    w[r] = li;
+}
+__global__ void k_scatter_vectors(const double* __restrict__ V, int64_t n, int64_t lda, const int* __restrict__ rank,
+                                  double* __restrict__ W) {
+    __shared__ double tile[32][33];
+    __shared__ int rk[32];
+    const int64_t i0 = (int64_t)blockIdx.y * 32, j0 = (int64_t)blockIdx.x * 32;
+    if (threadIdx.y == 0 && j0 + threadIdx.x < n) rk[threadIdx.x] = rank[j0 + threadIdx.x];
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t i = i0 + r, j = j0 + threadIdx.x;
+        if (i < n && j < n) tile[r][threadIdx.x] = V[i * lda + j];
+    }
+    __syncthreads();
+    // W[i][rank[j]] = V[i][j]
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t i = i0 + r, j = j0 + threadIdx.x;
+        if (i < n && j < n) W[i * n + rk[threadIdx.x]] = tile[r][threadIdx.x];
+    }
+}
+
+}  // namespace
+
+extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, G && w && W && n >= 1 && n <= 32768);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    const int64_t npad = ceil_div64(n, TS) * TS;
+    const int nb = (int)(npad / BS), P = nb / 2;
+    void* buf;
+    const size_t mat = (size_t)npad * npad * sizeof(double);
+    const size_t wbytes = (size_t)P * TS * TS * sizeof(double);
+    int rc = rt_scratch(h, 5, 2 * mat + wbytes + 1024, &buf);
+    if (rc) return rc;
+    double* A = (double*)buf;
+    double* V = A + npad * npad;
+    double* Wbuf = V + npad * npad;
+    double* maxdiag = Wbuf + (size_t)P * TS * TS;
+    unsigned long long* counter = (unsigned long long*)(maxdiag + 1);
+    int* rank;
+    rc = rt_scratch(h, 6, (size_t)n * sizeof(int), (void**)&rank);
+    if (rc) return rc;
+
+    k_pad_copy<<<dim3((unsigned)ceil_div64(npad, 256), (unsigned)npad), 256, 0, st>>>(G, n, A, V, npad);
+    RT_LAUNCH_CHECK(h);
+    k_maxdiag<<<1, 256, 0, st>>>(A, n, npad, maxdiag);
+    RT_LAUNCH_CHECK(h);
+    const int apply_smem = 3 * TS * LDS_ * (int)sizeof(double);
+    RT_CUDA(h, cudaFuncSetAttribute(k_jacobi_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, apply_smem));
+    const int sub_smem = 2 * TS * (TS + 1) * (int)sizeof(double);
+    RT_CUDA(h, cudaFuncSetAttribute(k_jacobi_sub, cudaFuncAttributeMaxDynamicSharedMemorySize, sub_smem));
+    const int nA = P * (P - 1) / 2, nV = (int)(npad / TS) * P;
+    const int rounds = nb - 1;
+    const int max_sweeps = 30;
+    int sweeps_used = -1;
+    for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+        RT_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st));
+        for (int round = 0; round < rounds; ++round) {
+            k_jacobi_sub<<<P, 256, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag);
+            RT_LAUNCH_CHECK(h);
+            k_jacobi_apply<<<nA + nV, 256, apply_smem, st>>>(A, V, npad, round, nb, Wbuf, nA);
+            RT_LAUNCH_CHECK(h);
+        }
+        unsigned long long rot = 0;
+        RT_CUDA(h, cudaMemcpyAsync(&rot, counter, sizeof(rot), cudaMemcpyDeviceToHost, st));
+        RT_CUDA(h, cudaStreamSynchronize(st));
+        if (rot == 0) { sweeps_used = sweep + 1; break; }
+    }
+    k_rank<<<(unsigned)ceil_div64(n, 128), 128, 0, st>>>(A, n, npad, rank, w);
+    RT_LAUNCH_CHECK(h);
+    k_scatter_vectors<<<dim3((unsigned)ceil_div64(n, 32), (unsigned)ceil_div64(n, 32)), dim3(32, 8), 0, st>>>(V, n, npad, rank, W);
+    RT_LAUNCH_CHECK(h);
+    if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps_used, sizeof(int), cudaMemcpyHostToDevice, st));
+    RT_CUDA(h, cudaStreamSynchronize(st));
+    if (sweeps_used < 0) return rt_fail(h, RT_ENOTCONV, "block Jacobi did not converge in %d sweeps (n=%lld)", max_sweeps, (long long)n);
+    return RT_OK;
+}

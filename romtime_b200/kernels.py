@@ -134,3 +134,18 @@ def pod_lift(S, Wr, order="F"):
                                             _ptr(Q), Q.stride(0), Q.stride(1), stream_ptr())
     check(rc, h, "rt_pod_lift_f64")
     return Q
+
+
+def sym_eig(G):
+    """rt_sym_eig_f64: (w descending, W with eigenvector k in column k, sweeps). G is destroyed."""
+    n = G.shape[0]
+    if not (G.is_contiguous() and G.dtype == F64):
+        G = G.contiguous().to(F64)
+    w = torch.empty(n, dtype=F64, device=G.device)
+    W = torch.empty((n, n), dtype=F64, device=G.device)
+    info = torch.zeros(1, dtype=torch.int32, device=G.device)
+    h = handle(G.device.index)
+    with torch.cuda.device(G.device):
+        rc = load_library().rt_sym_eig_f64(h, _ptr(G), n, _ptr(w), _ptr(W), _ptr(info), stream_ptr())
+    check(rc, h, "rt_sym_eig_f64")
+    return w, W, int(info.item())
