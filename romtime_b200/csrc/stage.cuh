@@ -6,7 +6,7 @@
 
 namespace dg {
 
-__global__ void k_stage_kmajor(const double* __restrict__ src, int64_t mn, int64_t k, int64_t smn, int64_t sk,
+static __global__ void k_stage_kmajor(const double* __restrict__ src, int64_t mn, int64_t k, int64_t smn, int64_t sk,
                                double* __restrict__ dst, int64_t ld) {
     __shared__ double tile[32][33];
     const int64_t k0 = (int64_t)blockIdx.x * 32, m0 = (int64_t)blockIdx.y * 32;

@@ -11,8 +11,24 @@
 //                                 accumulated rotation W_k;
 //              (2) k_jacobi_apply: A_kl <- W_k^T A_kl W_l for every tile pair k < l (DMMA, mirrored
 //                                 write keeps A exactly symmetric) and V[:, l] <- V[:, l] W_l.
-//   Converged when a whole sweep performs no rotation.  Rotation test: |a_pq| > eps*sqrt(|a_pp a_qq|).
-#include "common.cuh"
+//   Converged when a whole sweep performs no rotation.
+//   Rotation test: |a_pq| > max(eps*sqrt(|a_pp a_qq|), floor_rel*max|diag|).
+//
+// Plain Jacobi needs 20-30 sweeps on the rank-deficient, graded Gram matrices POD produces, so the
+// solver is PRECONDITIONED (Veselic-Hari / Drmac-Veselic):
+//   (a) k_pchol: diagonally pivoted Cholesky G ~= L L^T (n x r, r = numerical rank), one persistent
+//       cooperative kernel (warp per row, one grid barrier per column);
+//   (b) M = L^T L (r x r) on the TMA/DMMA GEMM core -- M is strongly diagonally dominant and graded;
+//   (c) block Jacobi on M (5-8 sweeps);   (d) W = L X diag(lambda)^-1/2 (GEMM core).
+// Eigenpairs below the pivoting tolerance (8 ulp of the largest diagonal entry -- the noise floor
+// of an fp64 Gram matrix) are returned as lambda = 0 with a zero vector.
+#include <cooperative_groups.h>
+
+#include <cstdlib>
+
+#include "gemm_util.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -51,7 +67,7 @@ __global__ void k_maxdiag(const double* __restrict__ A, int64_t n, int64_t lda, 
 // ---- (1) 64 x 64 sub-problem: cyclic two-sided Jacobi with parallel ordering, in shared memory ----
 __global__ void __launch_bounds__(256) k_jacobi_sub(double* __restrict__ A, int64_t lda, int round, int nb,
                                                     double* __restrict__ Wbuf, unsigned long long* rot_count,
-                                                    const double* __restrict__ maxdiag) {
+                                                    const double* __restrict__ maxdiag, double floor_rel) {
     constexpr int LD = TS + 1;
     extern __shared__ __align__(16) double sub_sm[];
     double* a = sub_sm;
@@ -71,7 +87,10 @@ __global__ void __launch_bounds__(256) k_jacobi_sub(double* __restrict__ A, int6
     }
     if (tid == 0) total = 0;
     __syncthreads();
-    const double floor_abs = 1e-26 * maxdiag[0];
+    // absolute floor (relative to the largest diagonal entry) below which entries are not rotated:
+    // a safeguard only -- M = L^T L from the pivoted Cholesky factor is a graded PSD matrix on which the
+    // relative test is stable, so the caller passes a tiny value
+    const double floor_abs = floor_rel * maxdiag[0];
 
     int prev_p = -1, prev_q = -1;
     for (int sweep = 0; sweep < 40; ++sweep) {
@@ -241,11 +260,11 @@ __global__ void __launch_bounds__(256) k_jacobi_apply(double* __restrict__ A, do
     }
 }
 
-__global__ void k_pad_copy(const double* __restrict__ G, int64_t n, double* __restrict__ A, double* __restrict__ V,
-                           int64_t npad) {
+__global__ void k_pad_copy(const double* __restrict__ G, int64_t n, int64_t ldg, double* __restrict__ A,
+                           double* __restrict__ V, int64_t npad) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
     if (j >= npad) return;
-    A[i * npad + j] = (i < n && j < n) ? G[i * n + j] : 0.0;
+    A[i * npad + j] = (i < n && j < n) ? G[i * ldg + j] : 0.0;
     V[i * npad + j] = (i == j) ? 1.0 : 0.0;
 }
 
@@ -263,7 +282,7 @@ __global__ void k_rank(const double* __restrict__ A, int64_t n, int64_t lda, int
     w[r] = li;
 }
 __global__ void k_scatter_vectors(const double* __restrict__ V, int64_t n, int64_t lda, const int* __restrict__ rank,
-                                  double* __restrict__ W) {
+                                  double* __restrict__ W, int64_t ldw) {
     __shared__ double tile[32][33];
     __shared__ int rk[32];
     const int64_t i0 = (int64_t)blockIdx.y * 32, j0 = (int64_t)blockIdx.x * 32;
@@ -276,17 +295,153 @@ __global__ void k_scatter_vectors(const double* __restrict__ V, int64_t n, int64
     // W[i][rank[j]] = V[i][j]
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
         const int64_t i = i0 + r, j = j0 + threadIdx.x;
-        if (i < n && j < n) W[i * n + rk[threadIdx.x]] = tile[r][threadIdx.x];
+        if (i < n && j < n) W[i * ldw + rk[threadIdx.x]] = tile[r][threadIdx.x];
     }
+}
+
+
+// ---- (a) diagonally pivoted Cholesky, one persistent cooperative kernel ----
+constexpr int kPcholThreads = 1024;
+struct PcholArgs {
+    const double* G;  // n x n symmetric, row-major, ld = n
+    int64_t n;
+    double* L;        // n x ldl row-major (zero-initialised); column k = k-th Cholesky column
+    int64_t ldl;
+    double* d;        // n: remaining diagonal
+    int* rank_out;
+    double tol;       // stop when max remaining diagonal <= tol * max initial diagonal
+    double* slot_val;
+    int64_t* slot_idx;
+};
+
+__device__ __forceinline__ void pc_merge(double& v, int64_t& i, double ov, int64_t oi) {
+    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+}
+
+__global__ void __launch_bounds__(kPcholThreads, 1) k_pchol(PcholArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) double rowj[];  // n
+    __shared__ double red_v[32];
+    __shared__ int64_t red_i[32];
+    __shared__ double piv_v;
+    __shared__ int64_t piv_i;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t n = a.n, ldl = a.ldl;
+    const int64_t gwarp = (int64_t)blockIdx.x * (kPcholThreads / 32) + warp;
+    const int64_t nwarps = (int64_t)gridDim.x * (kPcholThreads / 32);
+    double d0 = 0.0;
+    int k = 0;
+    for (;; ++k) {
+        // ---- local arg-max of the remaining diagonal (k == 0: initialise it from G) ----
+        double bv = -1.0;
+        int64_t bi = INT64_MAX;
+        if (k == 0) {
+            for (int64_t i = (int64_t)blockIdx.x * kPcholThreads + tid; i < n; i += (int64_t)gridDim.x * kPcholThreads) {
+                const double v = a.G[i * n + i];
+                a.d[i] = v;
+                pc_merge(bv, bi, v, i);
+            }
+        } else {
+            // column k-1:  l = (G[:, j] - L[:, :k-1] L[j, :k-1]^T) / sqrt(d_j), warp per row
+            const int64_t j = piv_i;
+            const double sq = sqrt(piv_v);
+            const int kc = k - 1;
+            for (int e = tid; e < kc; e += kPcholThreads) rowj[e] = a.L[j * ldl + e];
+            __syncthreads();
+            for (int64_t i = gwarp; i < n; i += nwarps) {
+                const double* Li = a.L + i * ldl;
+                double dot = 0.0;
+                for (int e = lane; e < kc; e += 32) dot = fma(Li[e], rowj[e], dot);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
+                if (lane == 0) {
+                    double col, dn;
+                    if (i == j) { col = sq; dn = 0.0; }
+                    else { col = (a.G[j * n + i] - dot) / sq; dn = a.d[i] - col * col; }
+                    a.L[i * ldl + kc] = col;
+                    a.d[i] = dn;
+                    pc_merge(bv, bi, dn, i);
+                }
+            }
+        }
+        // ---- CTA reduce -> slot -> grid barrier -> global reduce ----
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bv, off);
+            const int64_t oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            pc_merge(bv, bi, ov, oi);
+        }
+        if (lane == 0) { red_v[warp] = bv; red_i[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            double v = red_v[lane];
+            int64_t i = red_i[lane];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double ov = __shfl_xor_sync(0xffffffffu, v, off);
+                const int64_t oi = __shfl_xor_sync(0xffffffffu, i, off);
+                pc_merge(v, i, ov, oi);
+            }
+            if (lane == 0) {
+                a.slot_val[(size_t)(k & 1) * gridDim.x + blockIdx.x] = v;
+                a.slot_idx[(size_t)(k & 1) * gridDim.x + blockIdx.x] = i;
+            }
+        }
+        grid.sync();
+        if (warp == 0) {
+            double v = -1.0;
+            int64_t i = INT64_MAX;
+            for (unsigned s = lane; s < gridDim.x; s += 32)
+                pc_merge(v, i, __ldcg(a.slot_val + (size_t)(k & 1) * gridDim.x + s),
+                         __ldcg(a.slot_idx + (size_t)(k & 1) * gridDim.x + s));
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double ov = __shfl_xor_sync(0xffffffffu, v, off);
+                const int64_t oi = __shfl_xor_sync(0xffffffffu, i, off);
+                pc_merge(v, i, ov, oi);
+            }
+            if (lane == 0) { piv_v = v; piv_i = i; }
+        }
+        __syncthreads();
+        if (k == 0) d0 = piv_v;
+        if (k >= n || !(piv_v > a.tol * d0) || !(piv_v > 0.0)) break;
+    }
+    if (blockIdx.x == 0 && tid == 0) *a.rank_out = k;
+}
+
+__global__ void k_mirror_upper(double* __restrict__ M, int64_t n, int64_t ld) {
+    __shared__ double tile[32][33];
+    const int bi = blockIdx.y, bj = blockIdx.x;
+    if (bj < bi) return;
+    const int64_t i0 = (int64_t)bi * 32, j0 = (int64_t)bj * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t i = i0 + r, j = j0 + threadIdx.x;
+        tile[r][threadIdx.x] = (i < n && j < n) ? M[i * ld + j] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t j = j0 + r, i = i0 + threadIdx.x;
+        if (i < n && j < n && j > i) M[j * ld + i] = tile[threadIdx.x][r];
+    }
+}
+
+// X[:, c] *= 1/sqrt(lam_c) (zero column when lam_c <= 0);  w[c] = max(lam_c, 0)
+__global__ void k_scale_columns(double* __restrict__ X, int64_t r, int64_t ld, const double* __restrict__ lam,
+                                double* __restrict__ w) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, row = blockIdx.y;
+    if (c >= r) return;
+    const double l = lam[c];
+    const double sc = l > 0.0 ? rsqrt(l) : 0.0;
+    X[row * ld + c] *= sc;
+    if (row == 0) w[c] = l > 0.0 ? l : 0.0;
 }
 
 }  // namespace
 
-extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int* info, void* stream) {
-    if (!h) return RT_EINVAL;
-    RT_REQUIRE(h, G && w && W && n >= 1 && n <= 32768);
-    RT_CUDA(h, cudaSetDevice(h->device));
-    cudaStream_t st = rt_stream(stream);
+// Block Jacobi on a dense symmetric matrix Ain (n x n, row-major, leading dimension lda_in).
+// w (n, descending) and Wout (n x n row-major, leading dimension ldw, eigenvector k in column k).
+static int jacobi_eig(rt_handle* h, const double* Ain, int64_t n, int64_t lda_in, double* w, double* Wout, int64_t ldw,
+                      double floor_rel, int* sweeps_out, cudaStream_t st) {
     const int64_t npad = ceil_div64(n, TS) * TS;
     const int nb = (int)(npad / BS), P = nb / 2;
     void* buf;
@@ -303,7 +458,7 @@ extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, dou
     rc = rt_scratch(h, 6, (size_t)n * sizeof(int), (void**)&rank);
     if (rc) return rc;
 
-    k_pad_copy<<<dim3((unsigned)ceil_div64(npad, 256), (unsigned)npad), 256, 0, st>>>(G, n, A, V, npad);
+    k_pad_copy<<<dim3((unsigned)ceil_div64(npad, 256), (unsigned)npad), 256, 0, st>>>(Ain, n, lda_in, A, V, npad);
     RT_LAUNCH_CHECK(h);
     k_maxdiag<<<1, 256, 0, st>>>(A, n, npad, maxdiag);
     RT_LAUNCH_CHECK(h);
@@ -313,12 +468,12 @@ extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, dou
     RT_CUDA(h, cudaFuncSetAttribute(k_jacobi_sub, cudaFuncAttributeMaxDynamicSharedMemorySize, sub_smem));
     const int nA = P * (P - 1) / 2, nV = (int)(npad / TS) * P;
     const int rounds = nb - 1;
-    const int max_sweeps = 30;
+    const int max_sweeps = 60;
     int sweeps_used = -1;
     for (int sweep = 0; sweep < max_sweeps; ++sweep) {
         RT_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st));
         for (int round = 0; round < rounds; ++round) {
-            k_jacobi_sub<<<P, 256, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag);
+            k_jacobi_sub<<<P, 256, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag, floor_rel);
             RT_LAUNCH_CHECK(h);
             k_jacobi_apply<<<nA + nV, 256, apply_smem, st>>>(A, V, npad, round, nb, Wbuf, nA);
             RT_LAUNCH_CHECK(h);
@@ -326,14 +481,81 @@ extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, dou
         unsigned long long rot = 0;
         RT_CUDA(h, cudaMemcpyAsync(&rot, counter, sizeof(rot), cudaMemcpyDeviceToHost, st));
         RT_CUDA(h, cudaStreamSynchronize(st));
+        if (getenv("RT_EIG_DEBUG")) fprintf(stderr, "[rt_sym_eig] n=%lld sweep %d rotations %llu\n", (long long)n, sweep, rot);
         if (rot == 0) { sweeps_used = sweep + 1; break; }
     }
     k_rank<<<(unsigned)ceil_div64(n, 128), 128, 0, st>>>(A, n, npad, rank, w);
     RT_LAUNCH_CHECK(h);
-    k_scatter_vectors<<<dim3((unsigned)ceil_div64(n, 32), (unsigned)ceil_div64(n, 32)), dim3(32, 8), 0, st>>>(V, n, npad, rank, W);
+    k_scatter_vectors<<<dim3((unsigned)ceil_div64(n, 32), (unsigned)ceil_div64(n, 32)), dim3(32, 8), 0, st>>>(V, n, npad, rank, Wout, ldw);
     RT_LAUNCH_CHECK(h);
-    if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps_used, sizeof(int), cudaMemcpyHostToDevice, st));
-    RT_CUDA(h, cudaStreamSynchronize(st));
+    *sweeps_out = sweeps_used;
     if (sweeps_used < 0) return rt_fail(h, RT_ENOTCONV, "block Jacobi did not converge in %d sweeps (n=%lld)", max_sweeps, (long long)n);
+    return RT_OK;
+}
+
+extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, G && w && W && n >= 1 && n <= 16384);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+
+    // ---- (a) pivoted Cholesky  G ~= L L^T ----
+    const int64_t ldl = (n + 1) & ~int64_t(1);
+    double* L;
+    int rc = rt_scratch(h, 0, ((size_t)n * ldl + n + 8) * sizeof(double), (void**)&L);
+    if (rc) return rc;
+    double* d = L + (size_t)n * ldl;
+    int* rank_dev = (int*)(d + n);
+    PcholArgs a;
+    a.G = G; a.n = n; a.L = L; a.ldl = ldl; a.d = d; a.rank_out = rank_dev;
+    a.tol = 8.0 * kEps;
+    int grid = (int)ceil_div64(n, kPcholThreads / 32);
+    if (grid > h->sm_count) grid = h->sm_count;
+    void* slots;
+    rc = rt_scratch(h, 1, (size_t)grid * 2 * (sizeof(double) + sizeof(int64_t)), &slots);
+    if (rc) return rc;
+    a.slot_val = (double*)slots;
+    a.slot_idx = (int64_t*)((double*)slots + 2 * (size_t)grid);
+    const size_t smem = (size_t)n * sizeof(double) + 1024;
+    RT_CUDA(h, cudaFuncSetAttribute(k_pchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RT_CUDA(h, cudaMemsetAsync(L, 0, (size_t)n * ldl * sizeof(double), st));
+    void* params[] = {&a};
+    RT_CUDA(h, cudaLaunchCooperativeKernel((const void*)k_pchol, dim3(grid), dim3(kPcholThreads), params, smem, st));
+    RT_LAUNCH_CHECK(h);
+    int r = 0;
+    RT_CUDA(h, cudaMemcpyAsync(&r, rank_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(h, cudaStreamSynchronize(st));
+    if (getenv("RT_EIG_DEBUG")) fprintf(stderr, "[rt_sym_eig] n=%lld pivoted-Cholesky rank %d\n", (long long)n, r);
+    RT_CUDA(h, cudaMemsetAsync(w, 0, (size_t)n * sizeof(double), st));
+    RT_CUDA(h, cudaMemsetAsync(W, 0, (size_t)n * n * sizeof(double), st));
+    int sweeps = 0;
+    if (r > 0) {
+        // ---- (b) M = L^T L ----
+        const int64_t ldm = ((int64_t)r + 1) & ~int64_t(1);
+        double* M;
+        rc = rt_scratch(h, 4, ((size_t)2 * r * ldm + r) * sizeof(double), (void**)&M);
+        if (rc) return rc;
+        double* X = M + (size_t)r * ldm;
+        double* lam = X + (size_t)r * ldm;
+        dg::Operand opL{L, r, n, 1, ldl};  // (mn = column of L, k = row)
+        rc = gemm_tn(h, opL, opL, M, ldm, true, st);
+        if (rc) return rc;
+        k_mirror_upper<<<dim3((unsigned)ceil_div64(r, 32), (unsigned)ceil_div64(r, 32)), dim3(32, 8), 0, st>>>(M, r, ldm);
+        RT_LAUNCH_CHECK(h);
+        // ---- (c) block Jacobi on M ----
+        rc = jacobi_eig(h, M, r, ldm, lam, X, ldm, 1e-12 * kEps, &sweeps, st);
+        if (rc) return rc;
+        // ---- (d) W[:, :r] = L X diag(lam)^-1/2 ----
+        k_scale_columns<<<dim3((unsigned)ceil_div64(r, 256), (unsigned)r), 256, 0, st>>>(X, r, ldm, lam, w);
+        RT_LAUNCH_CHECK(h);
+        dg::Operand opA{L, n, r, ldl, 1};   // rows of L, k = pivot column
+        dg::Operand opB{X, r, r, 1, ldm};   // (mn = eigenvector index c, k): X[k][c]
+        dg::Params p = dg::default_params();
+        p.C = W; p.ldc_m = n; p.ldc_n = 1;
+        rc = dg::launch(h, opA, opB, p, st);
+        if (rc) return rc;
+    }
+    if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps, sizeof(int), cudaMemcpyHostToDevice, st));
+    RT_CUDA(h, cudaStreamSynchronize(st));
     return RT_OK;
 }

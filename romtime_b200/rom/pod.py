@@ -60,7 +60,9 @@ def orth_device(S, num=None, tol=None, normalize=True, allreduce=None):
         return Q, s, energy, W[:, :0].t(), {}
     idx = torch.as_tensor(keep, device=Sd.device)
     Wk = W.index_select(1, idx)                      # n x r
-    scale = torch.as_tensor(1.0 / s[keep], device=Sd.device)
+    sk = s[keep]
+    # modes below the rank-revealing tolerance come back as (0, zero vector): keep them zero
+    scale = torch.as_tensor(np.divide(1.0, sk, out=np.zeros_like(sk), where=sk > 0), device=Sd.device)
     Wr = Wk * scale                                   # columns scaled by 1/sigma
     if normalize:
         Wr = Wr / cn[:, None]                         # rows scaled by 1/||S_j||
