@@ -14,7 +14,7 @@ struct rt_handle {
     int smem_optin = 0;
     char err[512] = {0};
     // grow-only scratch buffers (slots so that independent kernels do not alias)
-    static constexpr int kSlots = 8;
+    static constexpr int kSlots = 12;
     void* ws[kSlots] = {nullptr};
     size_t ws_bytes[kSlots] = {0};
     int64_t launches = 0;

@@ -49,6 +49,9 @@ struct Params {
     int hook_kt;               // -1: disabled
     double* C2;
     double hook_scale;
+    // optional block-sparse K: k-tile range [x, y) per M-tile (device pointer, tiles_m entries);
+    // used for block-diagonal left operands (theta solve of all operators in one launch)
+    const int2* kt_ranges;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -160,8 +163,9 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
                 const int split = u / ntiles, tile = u % ntiles;
                 int tm, tn;
                 tile_coords(p, tile, tm, tn);
-                const int kt0 = split * p.kt_per_split;
-                const int kt1 = min(kt_total, kt0 + p.kt_per_split);
+                int kt0 = split * p.kt_per_split;
+                int kt1 = min(kt_total, kt0 + p.kt_per_split);
+                if (p.kt_ranges) { const int2 r = p.kt_ranges[tm]; kt0 = r.x; kt1 = min(kt_total, r.y); }
                 for (int kt = kt0; kt < kt1; ++kt) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], STAGE_BYTES);
@@ -202,8 +206,9 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
         const int split = u / ntiles, tile = u % ntiles;
         int tm, tn;
         tile_coords(p, tile, tm, tn);
-        const int kt0 = split * p.kt_per_split;
-        const int kt1 = min(kt_total, kt0 + p.kt_per_split);
+        int kt0 = split * p.kt_per_split;
+        int kt1 = min(kt_total, kt0 + p.kt_per_split);
+        if (p.kt_ranges) { const int2 r = p.kt_ranges[tm]; kt0 = r.x; kt1 = min(kt_total, r.y); }
 #pragma unroll
         for (int i = 0; i < MI; ++i)
 #pragma unroll

@@ -1,0 +1,536 @@
+// Online stage of the hyper-reduced ROM (reference rom/rom.py:430-555, :877-929; deim/deim.py:416-493):
+// theta solve, reduced-operator assembly and the batched implicit BDF sweep.
+//
+// Per time step and per chunk of parameters (Bc = 37*128 so that the assembly GEMM fills 148 SMs
+// in whole waves) the sweep launches
+//   k_state      : features phi(mu,t) (piston closed forms), u* and the BDF history vector w
+//   dgemm (TU)   : state-dependent part of the trilinear sampled entries  T u*
+//   k_entries    : sampled entries  f = scale * (C phi + b0 T u*)              (deim/deim.py:437-438)
+//   dgemm (theta): theta = PT_U^-1 f for all six reductors in ONE block-diagonal launch   (:491-492)
+//   dgemm (K)    : [K | M] = Theta^T Basis -- sum_q theta_q A_q^r for 5 operators, K = bdf M + dt(...)
+//                  accumulated in one pass; M is emitted at the k-boundary (hook)   (:445, rom.py:906)
+//   dgemm (f)    : reduced forcing  dt * basis_rhs theta_rhs
+//   k_lu_solve   : b = M w + f, dense LU with partial pivoting in shared memory, u = K^-1 b  (rom.py:492)
+// All GEMMs run on the TMA + DMMA core (dgemm_tma.cuh).  No collective: parameters are independent.
+#include "gemm_util.cuh"
+
+namespace {
+
+constexpr double kGamma = 1.4;  // fom/nonlinear.py:31
+constexpr int kNOps = 6;
+constexpr int kTril = 4;        // ops: mass, stiffness, convection, nonlinear_lifting, trilinear, rhs
+constexpr int kRhs = 5;
+
+// ------------------------------------------------------------------ small dense inverse
+// In-place Gauss-Jordan with partial pivoting in shared memory (one CTA), m <= 160.
+__global__ void __launch_bounds__(1024) k_invert(const double* __restrict__ A, int m, double* __restrict__ Ainv, int* info) {
+    extern __shared__ __align__(16) double sm[];
+    const int ld = m | 1;
+    double* a = sm;                                   // m * ld
+    int* piv = reinterpret_cast<int*>(a + (size_t)m * ld);  // m
+    __shared__ int prow;
+    __shared__ double pval;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int e = tid; e < m * m; e += nt) a[(e / m) * ld + (e % m)] = A[e];
+    __syncthreads();
+    for (int k = 0; k < m; ++k) {
+        if (tid < 32) {
+            double best = -1.0;
+            int bi = k;
+            for (int i = k + tid; i < m; i += 32) {
+                const double v = fabs(a[i * ld + k]);
+                if (v > best) { best = v; bi = i; }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double ov = __shfl_xor_sync(0xffffffffu, best, off);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+                if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+            }
+            if (tid == 0) {
+                prow = bi;
+                piv[k] = bi;
+                pval = a[bi * ld + k];
+                if (best == 0.0 && *info == 0) *info = k + 1;
+            }
+        }
+        __syncthreads();
+        const int p = prow;
+        if (p != k)
+            for (int j = tid; j < m; j += nt) { const double t = a[k * ld + j]; a[k * ld + j] = a[p * ld + j]; a[p * ld + j] = t; }
+        __syncthreads();
+        const double rinv = 1.0 / pval;
+        for (int j = tid; j < m; j += nt) a[k * ld + j] = (j == k) ? rinv : a[k * ld + j] * rinv;
+        __syncthreads();
+        // eliminate column k from every other row; column k receives -f * rinv
+        for (int e = tid; e < m * m; e += nt) {
+            const int i = e / m, j = e % m;
+            if (i == k || j == k) continue;
+            a[i * ld + j] = fma(-a[i * ld + k], a[k * ld + j], a[i * ld + j]);
+        }
+        __syncthreads();
+        for (int i = tid; i < m; i += nt)
+            if (i != k) a[i * ld + k] = -a[i * ld + k] * rinv;
+        __syncthreads();
+    }
+    // undo the row interchanges as column interchanges, in reverse order
+    for (int k = m - 1; k >= 0; --k) {
+        const int p = piv[k];
+        if (p != k)
+            for (int i = tid; i < m; i += nt) { const double t = a[i * ld + k]; a[i * ld + k] = a[i * ld + p]; a[i * ld + p] = t; }
+        __syncthreads();
+    }
+    for (int e = tid; e < m * m; e += nt) Ainv[e] = a[(e / m) * ld + (e % m)];
+}
+
+// ------------------------------------------------------------------ sweep plan
+struct SweepPlan {
+    int N, Npad, N2, ldk;       // ldk: row stride of K / M / basis_cat rows (even)
+    int m[kNOps], mpad[kNOps], qoff[kNOps + 1];
+    int Qmat, Qall;             // rows of the 5 matrix operators / all six (multiples of 16)
+    int evaluator;
+    int Bc, Bcpad;              // parameters in this chunk / padded row stride of q-major buffers
+};
+
+// phi(mu, t): problems/piston.py:18-60 ("rest" / "sudden"), fom/nonlinear.py:159-166 (b0),
+// :203-233 (lifting g = bL x / L), :277-299 (mesh velocity w = x L'/L)
+__device__ __forceinline__ void piston_features(int which, double a0, double om, double de, double t, double* phi) {
+    double L, dL, bL, dbL, s, c;
+    sincos(om * t, &s, &c);
+    if (which == 0) {
+        L = 1.0 - de * (1.0 - c);
+        dL = -om * de * s;
+        bL = -de * (om / a0) * s;
+        dbL = -de * om * (om / a0) * c;
+    } else {
+        L = 1.0 - de * s;
+        dL = -om * de * c;
+        bL = -de * (om / a0) * c;
+        dbL = de * om * (om / a0) * s;
+    }
+    const double b0 = (kGamma + 1.0) / 2.0 * a0;
+    phi[0] = 1.0; phi[1] = L; phi[2] = 1.0 / L; phi[3] = dL; phi[4] = a0; phi[5] = b0 * bL;
+    phi[6] = dbL * L; phi[7] = b0 * bL * bL; phi[8] = a0 * bL; phi[9] = dL * bL; phi[10] = bL / L; phi[11] = b0;
+}
+
+// Phi[f][p], Ustar[p][j] = u* (rom.py:897-901), Wv[p][j] = BDF history vector (rom.py:919-925)
+__global__ void k_state(SweepPlan pl, const double* __restrict__ mu, double t, int have_prev, int bdf2,
+                        const double* __restrict__ Un, const double* __restrict__ Unm1, double* __restrict__ Phi,
+                        double* __restrict__ Ustar, double* __restrict__ Wv) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < pl.Bc) {
+        double phi[RT_NF];
+        piston_features(pl.evaluator, mu[e * 3 + 0], mu[e * 3 + 1], mu[e * 3 + 2], t, phi);
+#pragma unroll
+        for (int f = 0; f < RT_NF; ++f) Phi[(int64_t)f * pl.Bcpad + e] = phi[f];
+    }
+    if (e < (int64_t)pl.Bc * pl.Npad) {
+        const double un = Un[e], um = Unm1[e];
+        Ustar[e] = have_prev ? 2.0 * un - um : un;
+        Wv[e] = bdf2 ? 2.0 * un - 0.5 * um : un;
+    }
+}
+
+// F[q][p] = scale_op * ( sum_f Ccat[q][f] Phi[f][p] + [trilinear] b0_p * TU[q - qoff][p] )
+__global__ void __launch_bounds__(256) k_entries(SweepPlan pl, const double* __restrict__ Ccat, const double* __restrict__ Phi,
+                                                 const double* __restrict__ TU, double dt, double* __restrict__ F) {
+    const int p = blockIdx.x * 256 + threadIdx.x;
+    if (p >= pl.Bc) return;
+    double phi[RT_NF];
+#pragma unroll
+    for (int f = 0; f < RT_NF; ++f) phi[f] = Phi[(int64_t)f * pl.Bcpad + p];
+    const int q0 = blockIdx.y * 32;
+    for (int q = q0; q < q0 + 32 && q < pl.Qall; ++q) {
+        int op = 0;
+        while (q >= pl.qoff[op + 1]) ++op;
+        if (q - pl.qoff[op] >= pl.m[op]) { F[(int64_t)q * pl.Bcpad + p] = 0.0; continue; }  // zero padding row
+        const double* c = Ccat + (int64_t)q * RT_NF;
+        double v = 0.0;
+#pragma unroll
+        for (int f = 0; f < RT_NF; ++f) v = fma(c[f], phi[f], v);
+        if (op == kTril && TU) v = fma(phi[11], TU[(int64_t)(q - pl.qoff[kTril]) * pl.Bcpad + p], v);
+        F[(int64_t)q * pl.Bcpad + p] = (op == 0) ? v : dt * v;
+    }
+}
+
+// ------------------------------------------------------------------ dense LU solve per parameter
+// One CTA per parameter: K (N x N) and the right-hand side b = M w + f as an augmented column in
+// shared memory, LU with partial pivoting (dgesv-like, replaces GMRES rom.py:36/:492), back
+// substitution by warp 0 with the solution in registers.  Also performs the BDF history shuffle
+// (rom.py:499-503) and writes the reduced solution (rom.py:537-549 "rom" storage).
+constexpr int kLuThreads = 256;
+
+template <int R>
+__global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const double* __restrict__ Kmat,
+                                                        const double* __restrict__ Mmat, const double* __restrict__ From,
+                                                        const double* __restrict__ Wv, double* __restrict__ Un,
+                                                        double* __restrict__ Unm1, double* __restrict__ uN_out,
+                                                        int64_t out_stride_p, int64_t out_off, int* __restrict__ info,
+                                                        int step) {
+    extern __shared__ __align__(16) double sm[];
+    const int N = pl.N, ld = (N + 1) | 1;  // odd leading dimension, column N holds b
+    double* a = sm;               // N * ld
+    double* rdiag = a + (size_t)N * ld;  // N
+    double* wv = rdiag + N;       // N
+    __shared__ int prow;
+    __shared__ int singular;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t p = blockIdx.x;
+    const double* Kp = Kmat + p * pl.ldk;
+    const double* Mp = Mmat + p * pl.ldk;
+    for (int e = tid; e < N * N; e += kLuThreads) a[(e / N) * ld + (e % N)] = Kp[e];
+    if (tid < N) wv[tid] = Wv[p * pl.Npad + tid];
+    if (tid == 0) singular = 0;
+    __syncthreads();
+    for (int i = warp; i < N; i += kLuThreads / 32) {
+        double dot = 0.0;
+        for (int j = lane; j < N; j += 32) dot = fma(Mp[i * N + j], wv[j], dot);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
+        if (lane == 0) a[i * ld + N] = dot + From[p * pl.Npad + i];
+    }
+    __syncthreads();
+    const int ty = tid >> 5, tx = lane;
+    for (int k = 0; k < N; ++k) {
+        if (warp == 0) {
+            double best = -1.0;
+            int bi = k;
+            for (int i = k + lane; i < N; i += 32) {
+                const double v = fabs(a[i * ld + k]);
+                if (v > best) { best = v; bi = i; }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double ov = __shfl_xor_sync(0xffffffffu, best, off);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+                if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+            }
+            if (lane == 0) { prow = bi; if (best == 0.0) singular = 1; }
+        }
+        __syncthreads();
+        const int pr = prow;
+        if (pr != k && tid <= N - k) {
+            const int j = k + tid;  // columns k..N (N = rhs)
+            const double t = a[k * ld + j]; a[k * ld + j] = a[pr * ld + j]; a[pr * ld + j] = t;
+        }
+        __syncthreads();
+        const double rinv = 1.0 / a[k * ld + k];
+        if (tid == 0) rdiag[k] = rinv;
+        for (int i = k + 1 + ty; i < N; i += kLuThreads / 32) {
+            const double l = a[i * ld + k] * rinv;
+            for (int j = k + 1 + tx; j <= N; j += 32) a[i * ld + j] = fma(-l, a[k * ld + j], a[i * ld + j]);
+        }
+        __syncthreads();
+    }
+    if (warp == 0) {
+        double bv[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { const int e = r * 32 + lane; bv[r] = e < N ? a[e * ld + N] : 0.0; }
+#pragma unroll
+        for (int kr = R - 1; kr >= 0; --kr) {
+            for (int kl = 31; kl >= 0; --kl) {
+                const int k = kr * 32 + kl;
+                if (k >= N) continue;
+                const double xk = __shfl_sync(0xffffffffu, bv[kr], kl) * rdiag[k];
+                if (lane == kl) bv[kr] = xk;
+#pragma unroll
+                for (int er = 0; er <= kr; ++er) {
+                    const int e = er * 32 + lane;
+                    if (e < k) bv[er] = fma(-a[e * ld + k], xk, bv[er]);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int e = r * 32 + lane;
+            if (e < N) {
+                const int64_t s = p * pl.Npad + e;
+                Unm1[s] = Un[s];
+                Un[s] = bv[r];
+                if (uN_out) uN_out[p * out_stride_p + out_off + e] = bv[r];
+            }
+        }
+        if (lane == 0 && singular && info[p] == 0) info[p] = step + 1;
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ stand-alone entry points
+extern "C" int rt_invert_f64(rt_handle* h, const double* A, int64_t m, double* Ainv, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, A && Ainv && info && m >= 1 && m <= 160);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    RT_CUDA(h, cudaMemsetAsync(info, 0, sizeof(int), st));
+    const int ld = (int)m | 1;
+    const size_t smem = (size_t)m * ld * sizeof(double) + (size_t)m * sizeof(int) + 16;
+    RT_CUDA(h, cudaFuncSetAttribute(k_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_invert<<<1, 1024, smem, st>>>(A, (int)m, Ainv, info);
+    RT_LAUNCH_CHECK(h);
+    return RT_OK;
+}
+
+extern "C" int rt_theta_f64(rt_handle* h, const double* PT_Uinv, int64_t m, const double* F, int64_t B, double* theta,
+                            void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, PT_Uinv && F && theta && m >= 1 && B >= 1);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    // theta[b][q'] = sum_q F[b][q] Inv[q'][q]
+    dg::Operand oa{F, B, m, m, 1}, ob{PT_Uinv, m, m, m, 1}, a, b;
+    int rc = dg::stage_if_needed(h, 3, oa, &a, st);
+    if (rc) return rc;
+    rc = dg::stage_if_needed(h, 4, ob, &b, st);
+    if (rc) return rc;
+    dg::Params p = dg::default_params();
+    p.C = theta; p.ldc_m = m; p.ldc_n = 1;
+    return dg::launch(h, a, b, p, st);
+}
+
+extern "C" int rt_assemble_batch_f64(rt_handle* h, const double* basis, int64_t R, int64_t m, int64_t b_stride_row,
+                                     int64_t b_stride_col, const double* theta, int64_t B, double* out, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, basis && theta && out && R >= 1 && m >= 1 && B >= 1);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    // out[b][r] = sum_q theta[b][q] basis[r][q]
+    dg::Operand oa{theta, B, m, m, 1}, ob{basis, R, m, b_stride_row, b_stride_col}, a, b;
+    int rc = dg::stage_if_needed(h, 3, oa, &a, st);
+    if (rc) return rc;
+    rc = dg::stage_if_needed(h, 4, ob, &b, st);
+    if (rc) return rc;
+    dg::Params p = dg::default_params();
+    p.C = out; p.ldc_m = R; p.ldc_n = 1;
+    return dg::launch(h, a, b, p, st);
+}
+
+// ------------------------------------------------------------------ the batched BDF sweep
+namespace {
+
+inline int64_t even64(int64_t x) { return (x + 1) & ~int64_t(1); }
+inline int64_t pad16(int64_t x) { return (x + 15) & ~int64_t(15); }
+
+struct Carver {
+    char* base;
+    size_t off = 0;
+    template <typename T>
+    T* take(size_t count) {
+        off = (off + 255) & ~size_t(255);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += count * sizeof(T);
+        return p;
+    }
+};
+
+struct SweepBuffers {
+    double *basis_cat, *basis_rhs, *Ccat, *Invcat, *Tpad;
+    int2* kt_ranges;
+    double *Phi, *Ustar, *Wv, *Un, *Unm1, *TU, *F, *Theta, *Kmat, *Mmat, *From;
+};
+
+size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
+    const size_t Bcp = pl.Bcpad;
+    b.basis_cat = c.take<double>((size_t)pl.Qmat * pl.ldk);
+    b.basis_rhs = c.take<double>((size_t)pl.mpad[kRhs] * pl.Npad);
+    b.Ccat = c.take<double>((size_t)pl.Qall * RT_NF);
+    b.Invcat = c.take<double>((size_t)pl.Qall * pl.Qall);
+    b.Tpad = c.take<double>((size_t)pl.mpad[kTril] * pl.Npad);
+    b.kt_ranges = c.take<int2>((size_t)(pl.Qall + 127) / 128);
+    const size_t setup_end = c.off;
+    b.Phi = c.take<double>(RT_NF * Bcp);
+    b.Ustar = c.take<double>(Bcp * pl.Npad);
+    b.Wv = c.take<double>(Bcp * pl.Npad);
+    b.Un = c.take<double>(Bcp * pl.Npad);
+    b.Unm1 = c.take<double>(Bcp * pl.Npad);
+    b.TU = c.take<double>((size_t)pl.mpad[kTril] * Bcp);
+    b.F = c.take<double>((size_t)pl.Qall * Bcp);
+    b.Theta = c.take<double>((size_t)pl.Qall * Bcp);
+    b.Kmat = c.take<double>(Bcp * pl.ldk);
+    b.Mmat = c.take<double>(Bcp * pl.ldk);
+    b.From = c.take<double>(Bcp * pl.Npad);
+    return setup_end;
+}
+
+template <int R>
+int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* uN_out, int64_t out_stride_p,
+              int64_t out_off, int* info, int step, cudaStream_t st) {
+    const int ld = (pl.N + 1) | 1;
+    const size_t smem = ((size_t)pl.N * ld + 2 * pl.N) * sizeof(double);
+    static bool attr_set[8] = {false};
+    if (!attr_set[R]) {
+        RT_CUDA(h, cudaFuncSetAttribute(k_lu_solve<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
+        attr_set[R] = true;
+    }
+    k_lu_solve<R><<<pl.Bc, kLuThreads, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, b.Un, b.Unm1, uN_out, out_stride_p,
+                                                   out_off, info, step);
+    RT_LAUNCH_CHECK(h);
+    return RT_OK;
+}
+
+int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, double dt, int bdf,
+               double* uN_out, double* uN_last, int* info, cudaStream_t st) {
+    RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1);
+    RT_REQUIRE(h, bdf == 1 || bdf == 2);
+    RT_REQUIRE(h, model->n_ops == kNOps);
+    RT_REQUIRE(h, model->N >= 1 && model->N <= 128);
+    RT_REQUIRE(h, model->evaluator == 0 || model->evaluator == 1);
+    SweepPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    pl.N = model->N;
+    pl.Npad = (int)even64(pl.N);
+    pl.N2 = pl.N * pl.N;
+    pl.ldk = (int)even64(pl.N2);
+    pl.evaluator = model->evaluator;
+    int off = 0;
+    for (int i = 0; i < kNOps; ++i) {
+        const rt_rom_operator& op = model->ops[i];
+        RT_REQUIRE(h, op.m >= 1 && op.basis_rom && op.PT_Uinv && op.C);
+        RT_REQUIRE(h, (i == kRhs) == (op.is_vector != 0));
+        RT_REQUIRE(h, op.ld >= (i == kRhs ? pl.N : pl.N2));
+        pl.m[i] = op.m;
+        pl.mpad[i] = (int)pad16(op.m);
+        pl.qoff[i] = off;
+        off += pl.mpad[i];
+    }
+    pl.qoff[kNOps] = off;
+    pl.Qall = off;
+    pl.Qmat = pl.qoff[kRhs];
+    const int64_t chunk = 37 * 128;  // 37*32 = 1184 = 8 * 148 output tiles per assembly GEMM
+    const int64_t Bc_max = B < chunk ? B : chunk;
+    pl.Bcpad = (int)(ceil_div64(Bc_max, 128) * 128);
+    pl.Bc = (int)Bc_max;
+
+    SweepBuffers b;
+    Carver sizing{nullptr};
+    carve(sizing, pl, b);
+    void* ws;
+    int rc = rt_scratch(h, 8, sizing.off + 1024, &ws);
+    if (rc) return rc;
+    Carver real{(char*)ws};
+    const size_t setup_bytes = carve(real, pl, b);
+
+    // ---- one-off model staging: concatenated, zero-padded operator tables ----
+    RT_CUDA(h, cudaMemsetAsync(ws, 0, setup_bytes, st));
+    for (int i = 0; i < kNOps; ++i) {
+        const rt_rom_operator& op = model->ops[i];
+        const int q0 = pl.qoff[i];
+        if (i != kRhs)
+            RT_CUDA(h, cudaMemcpy2DAsync(b.basis_cat + (size_t)q0 * pl.ldk, (size_t)pl.ldk * 8, op.basis_rom, (size_t)op.ld * 8,
+                                         (size_t)pl.N2 * 8, op.m, cudaMemcpyDeviceToDevice, st));
+        else
+            RT_CUDA(h, cudaMemcpy2DAsync(b.basis_rhs, (size_t)pl.Npad * 8, op.basis_rom, (size_t)op.ld * 8, (size_t)pl.N * 8,
+                                         op.m, cudaMemcpyDeviceToDevice, st));
+        RT_CUDA(h, cudaMemcpyAsync(b.Ccat + (size_t)q0 * RT_NF, op.C, (size_t)op.m * RT_NF * 8, cudaMemcpyDeviceToDevice, st));
+        RT_CUDA(h, cudaMemcpy2DAsync(b.Invcat + (size_t)q0 * pl.Qall + q0, (size_t)pl.Qall * 8, op.PT_Uinv, (size_t)op.m * 8,
+                                     (size_t)op.m * 8, op.m, cudaMemcpyDeviceToDevice, st));
+    }
+    const bool has_T = model->ops[kTril].T != nullptr;
+    if (has_T)
+        RT_CUDA(h, cudaMemcpy2DAsync(b.Tpad, (size_t)pl.Npad * 8, model->ops[kTril].T, (size_t)pl.N * 8, (size_t)pl.N * 8,
+                                     model->ops[kTril].m, cudaMemcpyDeviceToDevice, st));
+    {
+        // k-tile range of every 128-row tile of the block-diagonal inverse
+        const int tiles = (pl.Qall + 127) / 128;
+        int2 host_ranges[64];
+        RT_REQUIRE(h, tiles <= 64);
+        for (int t = 0; t < tiles; ++t) {
+            const int r0 = t * 128, r1 = (r0 + 128 < pl.Qall) ? r0 + 128 : pl.Qall;
+            int lo = pl.Qall, hi = 0;
+            for (int i = 0; i < kNOps; ++i) {
+                if (pl.qoff[i] < r1 && pl.qoff[i + 1] > r0) {
+                    if (pl.qoff[i] < lo) lo = pl.qoff[i];
+                    if (pl.qoff[i + 1] > hi) hi = pl.qoff[i + 1];
+                }
+            }
+            host_ranges[t] = make_int2(lo / 16, hi / 16);
+        }
+        RT_CUDA(h, cudaMemcpyAsync(b.kt_ranges, host_ranges, tiles * sizeof(int2), cudaMemcpyHostToDevice, st));
+        RT_CUDA(h, cudaStreamSynchronize(st));  // host_ranges is on the stack
+    }
+    RT_CUDA(h, cudaMemsetAsync(info, 0, (size_t)B * sizeof(int), st));
+
+    const int R = (pl.N + 31) / 32;
+    for (int64_t p0 = 0; p0 < B; p0 += chunk) {
+        pl.Bc = (int)((B - p0) < chunk ? (B - p0) : chunk);
+        const size_t state_bytes = (size_t)pl.Bcpad * pl.Npad * sizeof(double);
+        RT_CUDA(h, cudaMemsetAsync(b.Un, 0, state_bytes, st));    // zero initial condition (rom.py:451-452)
+        RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, state_bytes, st));  // uN_n1 = zeros, not None (rom.py:456-460)
+        const double* mu_c = mu + p0 * 3;
+        double t = 0.0;
+        for (int64_t n = 0; n < nt; ++n) {
+            t += dt;  // same accumulation as the reference loop (rom.py:476-479)
+            const int have_prev = (bdf == 2 && n > 0) ? 1 : 0;
+            const double bdfc = have_prev ? 1.5 : 1.0;  // first step uses bdf = 1.0 (rom.py:481-483)
+            const int64_t nstate = (int64_t)pl.Bc * pl.Npad;
+            k_state<<<(unsigned)ceil_div64(nstate, 256), 256, 0, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Phi,
+                                                                       b.Ustar, b.Wv);
+            RT_LAUNCH_CHECK(h);
+            if (has_T) {
+                dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
+                dg::Params p = dg::default_params();
+                p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
+                rc = dg::launch(h, oa, ob, p, st);
+                if (rc) return rc;
+            }
+            k_entries<<<dim3((unsigned)ceil_div64(pl.Bc, 256), (unsigned)ceil_div64(pl.Qall, 32)), 256, 0, st>>>(
+                pl, b.Ccat, b.Phi, has_T ? b.TU : nullptr, dt, b.F);
+            RT_LAUNCH_CHECK(h);
+            {   // theta = PT_U^-1 f, all reductors, block-diagonal
+                dg::Operand oa{b.Invcat, pl.Qall, pl.Qall, pl.Qall, 1}, ob{b.F, pl.Bc, pl.Qall, 1, pl.Bcpad};
+                dg::Params p = dg::default_params();
+                p.C = b.Theta; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
+                p.kt_ranges = b.kt_ranges;
+                rc = dg::launch(h, oa, ob, p, st);
+                if (rc) return rc;
+            }
+            {   // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
+                dg::Operand oa{b.Theta, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
+                dg::Params p = dg::default_params();
+                p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
+                p.C2 = b.Mmat; p.hook_kt = pl.mpad[0] / 16; p.hook_scale = bdfc;
+                rc = dg::launch(h, oa, ob, p, st);
+                if (rc) return rc;
+            }
+            {   // reduced forcing dt * basis_rhs theta_rhs
+                dg::Operand oa{b.Theta + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
+                dg::Operand ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
+                dg::Params p = dg::default_params();
+                p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
+                rc = dg::launch(h, oa, ob, p, st);
+                if (rc) return rc;
+            }
+            double* out = nullptr;
+            int64_t ostride = 0, ooff = 0;
+            if (uN_out) { out = uN_out + p0 * nt * pl.N; ostride = nt * pl.N; ooff = n * pl.N; }
+            else if (uN_last && n == nt - 1) { out = uN_last + p0 * pl.N; ostride = pl.N; ooff = 0; }
+            int* info_c = info + p0;
+            switch (R) {
+                case 1: rc = launch_lu<1>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
+                case 2: rc = launch_lu<2>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
+                case 3: rc = launch_lu<3>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
+                default: rc = launch_lu<4>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
+            }
+            if (rc) return rc;
+        }
+    }
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" int rt_online_sweep_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt,
+                                   double dt, int bdf, double* uN_out, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, uN_out);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    return sweep_impl(h, model, mu, B, nt, dt, bdf, uN_out, nullptr, info, rt_stream(stream));
+}
+
+extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt,
+                                        double dt, int bdf, double* uN_last, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, uN_last);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    return sweep_impl(h, model, mu, B, nt, dt, bdf, nullptr, uN_last, info, rt_stream(stream));
+}

@@ -6,8 +6,3 @@
 
 RT_WEAK int rt_project_vec_f64(rt_handle* h, const double*, int64_t, int64_t, const double*, int64_t, int64_t, int64_t, int64_t, int64_t, double*, void*) { NI(h); }
 RT_WEAK int rt_project_mat_f64(rt_handle* h, const double*, int64_t, int64_t, const int64_t*, const int64_t*, int64_t, const double*, int64_t, int64_t, int64_t, int64_t, int64_t, double*, int64_t, int64_t, void*) { NI(h); }
-RT_WEAK int rt_invert_f64(rt_handle* h, const double*, int64_t, double*, int*, void*) { NI(h); }
-RT_WEAK int rt_theta_f64(rt_handle* h, const double*, int64_t, const double*, int64_t, double*, void*) { NI(h); }
-RT_WEAK int rt_assemble_batch_f64(rt_handle* h, const double*, int64_t, int64_t, int64_t, int64_t, const double*, int64_t, double*, void*) { NI(h); }
-RT_WEAK int rt_online_sweep_f64(rt_handle* h, const rt_rom_model*, const double*, int64_t, int64_t, double, int, double*, int*, void*) { NI(h); }
-RT_WEAK int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model*, const double*, int64_t, int64_t, double, int, double*, int*, void*) { NI(h); }

@@ -149,3 +149,102 @@ def sym_eig(G):
         rc = load_library().rt_sym_eig_f64(h, _ptr(G), n, _ptr(w), _ptr(W), _ptr(info), stream_ptr())
     check(rc, h, "rt_sym_eig_f64")
     return w, W, int(info.item())
+
+
+# ------------------------------------------------------------------ theta / assembly / online sweep
+def invert(A):
+    """rt_invert_f64: inverse of a small dense matrix (m <= 160) by Gauss-Jordan with partial pivoting."""
+    Ad = to_device(A).contiguous()
+    m = Ad.shape[0]
+    Ainv = torch.empty_like(Ad)
+    info = torch.zeros(1, dtype=torch.int32, device=Ad.device)
+    h = handle(Ad.device.index)
+    with torch.cuda.device(Ad.device):
+        rc = load_library().rt_invert_f64(h, _ptr(Ad), m, _ptr(Ainv), _ptr(info), stream_ptr())
+    check(rc, h, "rt_invert_f64")
+    if int(info.item()) != 0:
+        raise np.linalg.LinAlgError("Singular matrix")
+    return Ainv
+
+
+def theta_batch(PT_Uinv, F):
+    """rt_theta_f64: theta[b] = PT_U^-1 F[b] for a batch F (B x m)."""
+    Fd = to_device(F).contiguous()
+    B, m = Fd.shape
+    out = torch.empty_like(Fd)
+    h = handle(Fd.device.index)
+    with torch.cuda.device(Fd.device):
+        rc = load_library().rt_theta_f64(h, _ptr(PT_Uinv), m, _ptr(Fd), B, _ptr(out), stream_ptr())
+    check(rc, h, "rt_theta_f64")
+    return out
+
+
+def assemble_batch(basis, theta):
+    """rt_assemble_batch_f64: out[b] = sum_q theta[b, q] basis[:, q]  (B x R)."""
+    Bd, Td = to_device(basis), to_device(theta).contiguous()
+    R, m = Bd.shape
+    B = Td.shape[0]
+    out = torch.empty((B, R), dtype=F64, device=Bd.device)
+    h = handle(Bd.device.index)
+    with torch.cuda.device(Bd.device):
+        rc = load_library().rt_assemble_batch_f64(h, _ptr(Bd), R, m, Bd.stride(0), Bd.stride(1), _ptr(Td), B, _ptr(out),
+                                                  stream_ptr())
+    check(rc, h, "rt_assemble_batch_f64")
+    return out
+
+
+OPS = ("mass", "stiffness", "convection", "nonlinear_lifting", "trilinear", "rhs")
+
+
+class DeviceRomModel:
+    """Device-resident hyper-reduced model (rt_rom_model): per operator basis_rom (column q contiguous),
+    PT_U^-1 (computed once with rt_invert_f64), evaluator tables C (m x 12) and T (m x N)."""
+
+    def __init__(self, model, device=None):
+        self.N = int(model["N"])
+        self.evaluator = 0 if model.get("which", "rest") == "rest" else 1
+        self._keep = []
+        self.struct = _lib.RomModel()
+        self.struct.N = self.N
+        self.struct.n_ops = len(OPS)
+        self.struct.evaluator = self.evaluator
+        for i, name in enumerate(OPS):
+            op = model[name]
+            basis = np.asfortranarray(np.asarray(op["basis_rom"], dtype=np.float64))  # column q contiguous
+            bd = to_device(basis)
+            inv = invert(np.ascontiguousarray(op["PT_U"], dtype=np.float64))
+            Cd = to_device(np.ascontiguousarray(op["C"], dtype=np.float64))
+            Td = None
+            if op.get("T") is not None:
+                Td = to_device(np.ascontiguousarray(op["T"], dtype=np.float64))
+            self._keep += [bd, inv, Cd, Td]
+            so = self.struct.ops[i]
+            so.m = basis.shape[1]
+            so.is_vector = 1 if name == "rhs" else 0
+            so.basis_rom = bd.data_ptr()
+            so.ld = int(bd.stride(1))
+            so.PT_Uinv = inv.data_ptr()
+            so.C = Cd.data_ptr()
+            so.T = Td.data_ptr() if Td is not None else None
+
+
+def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
+    """rt_online_sweep_f64 / rt_online_sweep_last_f64.  mus: (B, 3) [a0, omega, delta].
+    Returns (uN cuda tensor (B, nt, N) or (B, N), info int32 (B,))."""
+    md = to_device(mus).contiguous()
+    B = md.shape[0]
+    N = dev_model.N
+    info = torch.empty(B, dtype=torch.int32, device=md.device)
+    h = handle(md.device.index)
+    lib = load_library()
+    with torch.cuda.device(md.device):
+        if history:
+            out = torch.empty((B, nt, N), dtype=F64, device=md.device)
+            rc = lib.rt_online_sweep_f64(h, ctypes.byref(dev_model.struct), _ptr(md), B, nt, float(dt), int(bdf), _ptr(out),
+                                         _ptr(info), stream_ptr())
+        else:
+            out = torch.empty((B, N), dtype=F64, device=md.device)
+            rc = lib.rt_online_sweep_last_f64(h, ctypes.byref(dev_model.struct), _ptr(md), B, nt, float(dt), int(bdf),
+                                              _ptr(out), _ptr(info), stream_ptr())
+    check(rc, h, "rt_online_sweep_f64")
+    return out, info
