@@ -171,6 +171,14 @@ int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const doub
                              int64_t nt, double dt, int bdf, double* uN_last, int* info,
                              void* stream);
 
+/* Per-kernel-class device timing of the online sweep (CUDA events on the caller's stream around every
+ * launch of the first parameter chunk).  Classes: 0 state/features, 1 T u* GEMM, 2 sampled entries,
+ * 3 theta GEMM, 4 assembly GEMM (K and M), 5 forcing GEMM, 6 LU solve, 7 unused.
+ * rt_profile_read synchronises, returns accumulated milliseconds and launch counts, and resets. */
+#define RT_PROFILE_CLASSES 8
+int rt_profile_enable(rt_handle* h, int on);
+int rt_profile_read(rt_handle* h, double* ms, int64_t* launches);
+
 /* number of kernels launched by this handle since creation (bench.py "gpu_launches") */
 int64_t rt_launch_count(const rt_handle* h);
 

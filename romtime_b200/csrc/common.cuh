@@ -20,6 +20,7 @@ struct rt_handle {
     int64_t launches = 0;
     double fp64_peak = 0.0;
     void* tma_encode = nullptr;  // cuTensorMapEncodeTiled, resolved lazily
+    void* profile = nullptr;     // online-sweep profiler (online.cu)
 };
 
 inline int rt_fail(rt_handle* h, int code, const char* fmt, ...) {

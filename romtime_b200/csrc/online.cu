@@ -12,9 +12,36 @@
 //   dgemm (f)    : reduced forcing  dt * basis_rhs theta_rhs
 //   k_lu_solve   : b = M w + f, dense LU with partial pivoting in shared memory, u = K^-1 b  (rom.py:492)
 // All GEMMs run on the TMA + DMMA core (dgemm_tma.cuh).  No collective: parameters are independent.
+#include <utility>
+#include <vector>
+
 #include "gemm_util.cuh"
 
 namespace {
+
+// ---- optional per-kernel-class timing (rt_profile_enable / rt_profile_read) ----
+struct Profile {
+    bool on = false;
+    std::vector<cudaEvent_t> pool;
+    std::vector<int> cls;   // class of event pair i (events 2i, 2i+1)
+    size_t used = 0;        // pairs in flight
+    double ms[RT_PROFILE_CLASSES] = {0};
+    int64_t cnt[RT_PROFILE_CLASSES] = {0};
+};
+struct ProfScope {
+    Profile* p; cudaStream_t st; size_t idx;
+    ProfScope(Profile* prof, bool active, int c, cudaStream_t s) : p(active ? prof : nullptr), st(s), idx(0) {
+        if (!p) return;
+        if (p->pool.size() < 2 * (p->used + 1)) {
+            cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+            p->pool.push_back(a); p->pool.push_back(b); p->cls.push_back(c);
+        }
+        idx = p->used++;
+        p->cls[idx] = c;
+        cudaEventRecord(p->pool[2 * idx], st);
+    }
+    ~ProfScope() { if (p) cudaEventRecord(p->pool[2 * idx + 1], st); }
+};
 
 constexpr double kGamma = 1.4;  // fom/nonlinear.py:31
 constexpr int kNOps = 6;
@@ -254,6 +281,175 @@ __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const dou
     }
 }
 
+// ------------------------------------------------------------------ register-resident LU (N <= 64)
+// The shared-memory LU above is bound by shared-memory bandwidth (3 accesses per FMA).  Here every
+// thread keeps ONE ROW of [K | b] in registers (NP + 1 doubles, NP = 32 or 64 = threads per CTA; rows
+// and columns beyond N are identity padding).  Per elimination step: warp-shuffle arg-max of the
+// pivot column among unpivoted rows (implicit partial pivoting, first maximum like dgetrf), the
+// winning thread of each warp publishes its row in shared memory, ONE barrier, every unpivoted row
+// updates itself with broadcast (conflict-free) reads.  U rows are then written in pivot order and
+// warp 0 back-substitutes.
+// coalesced staging of an N x N row-major matrix into padded shared memory: warp w takes rows w, w+NW, ...;
+// 16 rows (32 loads per lane) are issued before the first store so that one round trip covers them
+template <int NW, int LD>
+__device__ __forceinline__ void stage_matrix(double* __restrict__ stage, const double* __restrict__ src, int N, int warp, int lane) {
+    for (int i0 = warp; i0 < N; i0 += 16 * NW) {
+        double v0[16], v1[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int i = i0 + u * NW;
+            v0[u] = (i < N && lane < N) ? __ldg(src + i * N + lane) : 0.0;
+            v1[u] = (i < N && lane + 32 < N) ? __ldg(src + i * N + lane + 32) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            const int i = i0 + u * NW;
+            if (i < N && lane < N) stage[i * LD + lane] = v0[u];
+            if (i < N && lane + 32 < N) stage[i * LD + lane + 32] = v1[u];
+        }
+    }
+}
+
+// one elimination step with compile-time k (keeps the row in registers: every index is static)
+template <int NP, int K>
+__device__ __forceinline__ void lu_step(double (&r)[NP + 1], bool& done, bool& sing, int& order, double* piv,
+                                        unsigned long long (*cand)[NP / 32], int t, int lane, int warp) {
+    constexpr int NW = NP / 32;
+    constexpr int PV = NP + 2;
+    // arg-max key: |r_k| with the 7 low mantissa bits replaced by (candidate flag, 63 - t): the largest
+    // magnitude wins, the lowest row index on (near-)ties; two redux.sync instead of a shuffle tree
+    const unsigned long long key =
+        done ? 0ull : ((unsigned long long)__double_as_longlong(fabs(r[K])) & ~127ull) | 64ull | (unsigned long long)(63 - t);
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    constexpr int par = K & 1;
+    double* mine = piv + (par * NW + warp) * PV;
+    if (lo == ml && hi == mh && !done) {
+        // warp winner publishes its row [K..NP] plus the reciprocal pivot in slot NP+1 (16-byte stores)
+        const double rinv = 1.0 / r[K];
+#pragma unroll
+        for (int j2 = (K & ~1); j2 < NP; j2 += 2) *reinterpret_cast<double2*>(mine + j2) = make_double2(r[j2], r[j2 + 1]);
+        *reinterpret_cast<double2*>(mine + NP) = make_double2(r[NP], rinv);
+    }
+    if (lane == 0) cand[par][warp] = ((unsigned long long)mh << 32) | ml;
+    __syncthreads();
+    int ww = 0;
+    unsigned long long gk = cand[par][0];
+#pragma unroll
+    for (int w = 1; w < NW; ++w)
+        if (cand[par][w] > gk) { gk = cand[par][w]; ww = w; }
+    const int gt = 63 - (int)(gk & 63ull);
+    const double* pr = piv + (par * NW + ww) * PV;
+    if (t == gt) {
+        done = true;
+        order = K;
+        if (r[K] == 0.0) sing = true;
+    } else if (!done) {
+        const double2 tail = *reinterpret_cast<const double2*>(pr + NP);
+        const double l = r[K] * tail.y;
+        if ((K & 1) == 0) r[K + 1] = fma(-l, pr[K + 1], r[K + 1]);
+#pragma unroll
+        for (int j2 = ((K + 2) & ~1); j2 < NP; j2 += 2) {
+            const double2 q = *reinterpret_cast<const double2*>(pr + j2);
+            r[j2] = fma(-l, q.x, r[j2]);
+            r[j2 + 1] = fma(-l, q.y, r[j2 + 1]);
+        }
+        r[NP] = fma(-l, tail.x, r[NP]);
+    }
+}
+template <int NP, int... Ks>
+__device__ __forceinline__ void lu_steps(double (&r)[NP + 1], bool& done, bool& sing, int& order, double* piv,
+                                         unsigned long long (*cand)[NP / 32], int t, int lane, int warp,
+                                         std::integer_sequence<int, Ks...>) {
+    (lu_step<NP, Ks>(r, done, sing, order, piv, cand, t, lane, warp), ...);
+}
+
+template <int NP>
+__global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl, const double* __restrict__ Kmat,
+                                                                 const double* __restrict__ Mmat,
+                                                                 const double* __restrict__ From, const double* __restrict__ Wv,
+                                                                 double* __restrict__ Un, double* __restrict__ Unm1,
+                                                                 double* __restrict__ uN_out, int64_t out_stride_p,
+                                                                 int64_t out_off, int* __restrict__ info, int step) {
+    constexpr int LD = NP + 1;
+    constexpr int NW = NP / 32;
+    constexpr int PV = NP + 2;
+    extern __shared__ __align__(16) double sm[];
+    double* piv = sm;                        // 2 * NW * PV   (16-byte aligned rows)
+    double* wv = piv + 2 * NW * PV;          // NP
+    double* rdiag = wv + NP;                 // NP
+    double* stage = rdiag + NP;              // NP * LD
+    __shared__ unsigned long long cand[2][NW];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int N = pl.N;
+    const int64_t p = blockIdx.x;
+    const double* Kp = Kmat + p * pl.ldk;
+    const double* Mp = Mmat + p * pl.ldk;
+
+    stage_matrix<NW, LD>(stage, Mp, N, warp, lane);
+    wv[t] = t < N ? Wv[p * pl.Npad + t] : 0.0;
+    __syncthreads();
+    double bt = 0.0;
+    if (t < N) {
+        double b0 = 0.0, b1 = 0.0;
+        int j = 0;
+        for (; j + 1 < N; j += 2) { b0 = fma(stage[t * LD + j], wv[j], b0); b1 = fma(stage[t * LD + j + 1], wv[j + 1], b1); }
+        if (j < N) b0 = fma(stage[t * LD + j], wv[j], b0);
+        bt = (b0 + b1) + From[p * pl.Npad + t];
+    }
+    __syncthreads();
+    stage_matrix<NW, LD>(stage, Kp, N, warp, lane);
+    __syncthreads();
+    double r[NP + 1];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) r[j] = (t < N && j < N) ? stage[t * LD + j] : (j == t ? 1.0 : 0.0);
+    r[NP] = bt;
+    __syncthreads();
+
+    bool done = false, sing = false;
+    int order = 0;
+    lu_steps<NP>(r, done, sing, order, piv, cand, t, lane, warp, std::make_integer_sequence<int, NP>{});
+    // U rows (and the transformed right-hand side) in pivot order
+#pragma unroll
+    for (int j = 0; j <= NP; ++j)
+        if (j >= order) stage[order * LD + j] = r[j];
+#pragma unroll
+    for (int j = 0; j < NP; ++j)
+        if (j == order) rdiag[order] = 1.0 / r[j];
+    __syncthreads();
+    if (warp == 0) {
+        double xv[NW];
+#pragma unroll
+        for (int q = 0; q < NW; ++q) xv[q] = stage[(q * 32 + lane) * LD + NP];
+#pragma unroll
+        for (int kr = NW - 1; kr >= 0; --kr) {
+#pragma unroll 4
+            for (int kl = 31; kl >= 0; --kl) {
+                const int k = kr * 32 + kl;
+                const double xk = __shfl_sync(0xffffffffu, xv[kr], kl) * rdiag[k];
+                if (lane == kl) xv[kr] = xk;
+#pragma unroll
+                for (int er = 0; er <= kr; ++er) {
+                    const int e = er * 32 + lane;
+                    if (e < k) xv[er] = fma(-stage[e * LD + k], xk, xv[er]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < NW; ++q) {
+            const int e = q * 32 + lane;
+            if (e < N) {
+                const int64_t s = p * pl.Npad + e;
+                Unm1[s] = Un[s];
+                Un[s] = xv[q];
+                if (uN_out) uN_out[p * out_stride_p + out_off + e] = xv[q];
+            }
+        }
+    }
+    if (sing) atomicCAS(&info[p], 0, step + 1);
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------ stand-alone entry points
@@ -368,6 +564,21 @@ int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* 
     return RT_OK;
 }
 
+template <int NP>
+int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* uN_out, int64_t out_stride_p,
+                  int64_t out_off, int* info, int step, cudaStream_t st) {
+    const size_t smem = ((size_t)NP * (NP + 1) + 2 * (NP / 32) * (NP + 2) + 2 * NP) * sizeof(double) + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        RT_CUDA(h, cudaFuncSetAttribute(k_lu_reg<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        attr_set = true;
+    }
+    k_lu_reg<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, b.Un, b.Unm1, uN_out, out_stride_p, out_off,
+                                          info, step);
+    RT_LAUNCH_CHECK(h);
+    return RT_OK;
+}
+
 int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, double dt, int bdf,
                double* uN_out, double* uN_last, int* info, cudaStream_t st) {
     RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1);
@@ -463,20 +674,27 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
             const int have_prev = (bdf == 2 && n > 0) ? 1 : 0;
             const double bdfc = have_prev ? 1.5 : 1.0;  // first step uses bdf = 1.0 (rom.py:481-483)
             const int64_t nstate = (int64_t)pl.Bc * pl.Npad;
+            Profile* prof = (Profile*)h->profile;
+            const bool pa = prof && prof->on && p0 == 0;
+            { ProfScope ps(prof, pa, 0, st);
             k_state<<<(unsigned)ceil_div64(nstate, 256), 256, 0, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Phi,
                                                                        b.Ustar, b.Wv);
+            }
             RT_LAUNCH_CHECK(h);
             if (has_T) {
+                ProfScope ps(prof, pa, 1, st);
                 dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
                 dg::Params p = dg::default_params();
                 p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
                 rc = dg::launch(h, oa, ob, p, st);
                 if (rc) return rc;
             }
+            { ProfScope ps(prof, pa, 2, st);
             k_entries<<<dim3((unsigned)ceil_div64(pl.Bc, 256), (unsigned)ceil_div64(pl.Qall, 32)), 256, 0, st>>>(
                 pl, b.Ccat, b.Phi, has_T ? b.TU : nullptr, dt, b.F);
+            }
             RT_LAUNCH_CHECK(h);
-            {   // theta = PT_U^-1 f, all reductors, block-diagonal
+            {   ProfScope ps(prof, pa, 3, st);  // theta = PT_U^-1 f, all reductors, block-diagonal
                 dg::Operand oa{b.Invcat, pl.Qall, pl.Qall, pl.Qall, 1}, ob{b.F, pl.Bc, pl.Qall, 1, pl.Bcpad};
                 dg::Params p = dg::default_params();
                 p.C = b.Theta; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
@@ -484,7 +702,7 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
                 rc = dg::launch(h, oa, ob, p, st);
                 if (rc) return rc;
             }
-            {   // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
+            {   ProfScope ps(prof, pa, 4, st);  // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
                 dg::Operand oa{b.Theta, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
                 dg::Params p = dg::default_params();
                 p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
@@ -492,7 +710,7 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
                 rc = dg::launch(h, oa, ob, p, st);
                 if (rc) return rc;
             }
-            {   // reduced forcing dt * basis_rhs theta_rhs
+            {   ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
                 dg::Operand oa{b.Theta + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
                 dg::Operand ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
                 dg::Params p = dg::default_params();
@@ -505,7 +723,10 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
             if (uN_out) { out = uN_out + p0 * nt * pl.N; ostride = nt * pl.N; ooff = n * pl.N; }
             else if (uN_last && n == nt - 1) { out = uN_last + p0 * pl.N; ostride = pl.N; ooff = 0; }
             int* info_c = info + p0;
-            switch (R) {
+            ProfScope ps_lu(prof, pa, 6, st);
+            if (pl.N <= 32) rc = launch_lu_reg<32>(h, pl, b, out, ostride, ooff, info_c, (int)n, st);
+            else if (pl.N <= 64) rc = launch_lu_reg<64>(h, pl, b, out, ostride, ooff, info_c, (int)n, st);
+            else switch (R) {
                 case 1: rc = launch_lu<1>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
                 case 2: rc = launch_lu<2>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
                 case 3: rc = launch_lu<3>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
@@ -533,4 +754,30 @@ extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model,
     RT_REQUIRE(h, uN_last);
     RT_CUDA(h, cudaSetDevice(h->device));
     return sweep_impl(h, model, mu, B, nt, dt, bdf, nullptr, uN_last, info, rt_stream(stream));
+}
+
+extern "C" int rt_profile_enable(rt_handle* h, int on) {
+    if (!h) return RT_EINVAL;
+    if (!h->profile) h->profile = new Profile();
+    ((Profile*)h->profile)->on = on != 0;
+    return RT_OK;
+}
+
+extern "C" int rt_profile_read(rt_handle* h, double* ms, int64_t* launches) {
+    if (!h || !ms || !launches) return RT_EINVAL;
+    RT_CUDA(h, cudaSetDevice(h->device));
+    RT_CUDA(h, cudaDeviceSynchronize());
+    Profile* p = (Profile*)h->profile;
+    for (int c = 0; c < RT_PROFILE_CLASSES; ++c) { ms[c] = 0; launches[c] = 0; }
+    if (!p) return RT_OK;
+    for (size_t i = 0; i < p->used; ++i) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, p->pool[2 * i], p->pool[2 * i + 1]) == cudaSuccess) {
+            p->ms[p->cls[i]] += t;
+            p->cnt[p->cls[i]] += 1;
+        }
+    }
+    p->used = 0;
+    for (int c = 0; c < RT_PROFILE_CLASSES; ++c) { ms[c] = p->ms[c]; launches[c] = p->cnt[c]; p->ms[c] = 0; p->cnt[c] = 0; }
+    return RT_OK;
 }

@@ -248,3 +248,20 @@ def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
                                               _ptr(out), _ptr(info), stream_ptr())
     check(rc, h, "rt_online_sweep_f64")
     return out, info
+
+
+PROFILE_CLASSES = ("state", "gemm_Tu", "entries", "gemm_theta", "gemm_assembly", "gemm_forcing", "lu_solve", "unused")
+
+
+def profile_enable(on=True):
+    h = handle()
+    check(load_library().rt_profile_enable(h, int(bool(on))), h, "rt_profile_enable")
+
+
+def profile_read():
+    """{class: (milliseconds, launches)} accumulated since the last read (first chunk of each sweep)."""
+    h = handle()
+    ms = (ctypes.c_double * 8)()
+    cnt = (ctypes.c_int64 * 8)()
+    check(load_library().rt_profile_read(h, ms, cnt), h, "rt_profile_read")
+    return {name: (ms[i], int(cnt[i])) for i, name in enumerate(PROFILE_CLASSES) if cnt[i]}
