@@ -18,6 +18,8 @@ F64 = torch.float64
 
 def to_device(a, dtype=F64):
     """NumPy / torch (any device) -> CUDA tensor, strides preserved (C- and F-order both kept)."""
+    if not torch.cuda.is_available():
+        raise _lib.RomtimeB200Error("romtime_b200 needs a B200 (sm_100a) GPU: there is no CPU fallback")
     if isinstance(a, torch.Tensor):
         t = a
     else:
