@@ -286,7 +286,8 @@ def main():
     roof = None
     if "gemm_assembly" in prof:
         g_ms, g_n = prof["gemm_assembly"]
-        chunk = min(Bl, 37 * 128)
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        chunk = min(Bl, int(kernels.load_library().rt_sweep_chunk(Bl, N, sms)))
         flops = 2.0 * chunk * (N * N) * (5 * ((m + 15) // 16 * 16))
         ach = flops / (g_ms / g_n) * 1e-9
         total_prof = sum(v[0] for v in prof.values())

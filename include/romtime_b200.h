@@ -171,6 +171,12 @@ int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const doub
                              int64_t nt, double dt, int bdf, double* uN_last, int* info,
                              void* stream);
 
+/* Host-only helper (no device work): parameters per chunk the sweep uses for a batch of B parameters,
+ * reduced dimension N, on a device with sm_count SMs -- a multiple of 128 chosen so that the assembly
+ * GEMM's output tiles fill whole waves of sm_count CTAs.  Exposed for tests and for callers that want
+ * to size parameter shards (multi-GPU: romtime_b200/distributed.py). */
+int64_t rt_sweep_chunk(int64_t B, int N, int sm_count);
+
 /* Per-kernel-class device timing of the online sweep (CUDA events on the caller's stream around every
  * launch of the first parameter chunk).  Classes: 0 state/features, 1 T u* GEMM, 2 sampled entries,
  * 3 theta GEMM, 4 assembly GEMM (K and M), 5 forcing GEMM, 6 LU solve, 7 unused.

@@ -507,6 +507,24 @@ namespace {
 inline int64_t even64(int64_t x) { return (x + 1) & ~int64_t(1); }
 inline int64_t pad16(int64_t x) { return (x + 15) & ~int64_t(15); }
 
+// Parameters per chunk.  The assembly GEMM has (chunk/128) x tiles_n output tiles on `sms` persistent CTAs;
+// the chunk (a multiple of 128, at most 40*128 so that the K/M buffers stay ~330 MB) is chosen to
+// minimise the total number of tile waves over the whole batch, i.e. the wave-quantisation loss of the
+// dominant kernel: 37*128 parameters x 32 tiles = 8 full waves of 148 for N = 64 on a B200.
+int64_t plan_chunk(int64_t B, int tiles_n, int sms) {
+    const int64_t rows_total = ceil_div64(B, 128);
+    int64_t best_k = 1;
+    double best_cost = 1e300;
+    for (int64_t k = 1; k <= 40; ++k) {
+        const int64_t nfull = rows_total / k, rem = rows_total - nfull * k;
+        const double waves = (double)nfull * (double)ceil_div64(k * tiles_n, sms) + (double)ceil_div64(rem * tiles_n, sms);
+        const double chunks = (double)(nfull + (rem ? 1 : 0));
+        const double cost = waves + 0.25 * chunks;  // per-chunk-step fixed cost of the small kernels, in waves
+        if (cost < best_cost - 1e-9) { best_cost = cost; best_k = k; }
+    }
+    return best_k * 128;
+}
+
 struct Carver {
     char* base;
     size_t off = 0;
@@ -607,7 +625,7 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
     pl.qoff[kNOps] = off;
     pl.Qall = off;
     pl.Qmat = pl.qoff[kRhs];
-    const int64_t chunk = 37 * 128;  // 37*32 = 1184 = 8 * 148 output tiles per assembly GEMM
+    const int64_t chunk = plan_chunk(B, (pl.N2 + dg::BN - 1) / dg::BN, h->sm_count);
     const int64_t Bc_max = B < chunk ? B : chunk;
     pl.Bcpad = (int)(ceil_div64(Bc_max, 128) * 128);
     pl.Bc = (int)Bc_max;
@@ -754,6 +772,11 @@ extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model,
     RT_REQUIRE(h, uN_last);
     RT_CUDA(h, cudaSetDevice(h->device));
     return sweep_impl(h, model, mu, B, nt, dt, bdf, nullptr, uN_last, info, rt_stream(stream));
+}
+
+extern "C" int64_t rt_sweep_chunk(int64_t B, int N, int sm_count) {
+    if (B < 1 || N < 1 || sm_count < 1) return 0;
+    return plan_chunk(B, (int)ceil_div64((int64_t)N * N, dg::BN), sm_count);
 }
 
 extern "C" int rt_profile_enable(rt_handle* h, int on) {

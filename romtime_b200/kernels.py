@@ -153,6 +153,46 @@ def sym_eig(G):
     return w, W, int(info.item())
 
 
+# ------------------------------------------------------------------ projections onto the reduced basis
+def project_vec(V, U):
+    """rt_project_vec_f64: DEIM.project_basis, out (N x m) = V^T U."""
+    Vd, Ud = to_device(V), to_device(U)
+    Nh, N = Vd.shape
+    Nh2, m = Ud.shape
+    if Nh != Nh2:
+        raise ValueError(f"V has {Nh} rows, the collateral basis has {Nh2}")
+    out = torch.empty((N, m), dtype=F64, device=Vd.device)
+    h = handle(Vd.device.index)
+    with torch.cuda.device(Vd.device):
+        rc = load_library().rt_project_vec_f64(h, _ptr(Vd), Vd.stride(0), Vd.stride(1), _ptr(Ud), Ud.stride(0),
+                                               Ud.stride(1), Nh, N, m, _ptr(out), stream_ptr())
+    check(rc, h, "rt_project_vec_f64")
+    return out
+
+
+def project_mat(U, rows, cols, V):
+    """rt_project_mat_f64: MDEIM.project_basis, out (N^2 x m, F-order: column q contiguous) with
+    out[i*N + j, q] = (V^T csr(U[:, q]; rows, cols) V)[i, j]."""
+    Ud, Vd = to_device(U), to_device(V)
+    nnz, m = Ud.shape
+    Nh, N = Vd.shape
+    rows_h = np.asarray(rows, dtype=np.int64).reshape(-1)
+    cols_h = np.asarray(cols, dtype=np.int64).reshape(-1)
+    if rows_h.shape[0] != nnz or cols_h.shape[0] != nnz:
+        raise ValueError("rows/cols must have one entry per row of the collateral basis")
+    if nnz and (rows_h.min() < 0 or cols_h.min() < 0 or rows_h.max() >= Nh or cols_h.max() >= Nh):
+        raise ValueError("matrix topology does not fit the reduced basis (row/column index out of range)")
+    rd, cd = to_device(rows_h, torch.int64), to_device(cols_h, torch.int64)
+    out = torch.empty((m, N * N), dtype=F64, device=Ud.device).t()
+    h = handle(Ud.device.index)
+    with torch.cuda.device(Ud.device):
+        rc = load_library().rt_project_mat_f64(h, _ptr(Ud), Ud.stride(0), Ud.stride(1), _ptr(rd), _ptr(cd), nnz, _ptr(Vd),
+                                               Vd.stride(0), Vd.stride(1), Nh, N, m, _ptr(out), out.stride(0),
+                                               out.stride(1), stream_ptr())
+    check(rc, h, "rt_project_mat_f64")
+    return out
+
+
 # ------------------------------------------------------------------ theta / assembly / online sweep
 def invert(A):
     """rt_invert_f64: inverse of a small dense matrix (m <= 160) by Gauss-Jordan with partial pivoting."""
