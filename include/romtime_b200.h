@@ -136,7 +136,7 @@ int rt_assemble_batch_f64(rt_handle* h, const double* basis, int64_t R, int64_t 
 /* ---------------------------------------------- online sweep (rom/rom.py:430-555) ------ */
 /* One hyper-reduced operator of the ROM (a DEIM/MDEIM/N-MDEIM reductor after project_basis). */
 typedef struct {
-    int32_t m;               /* collateral basis size (deim N)                                     */
+    int32_t m;               /* collateral basis size (deim N); 0 = operator absent                */
     int32_t is_vector;       /* 0: matrix operator (basis_rom is N*N x m), 1: vector (N x m)       */
     const double* basis_rom; /* column q contiguous: element (r, q) at basis_rom[q * ld + r]       */
     int64_t ld;              /* leading dimension of basis_rom (>= N*N or N)                       */
@@ -170,6 +170,24 @@ int rt_online_sweep_f64(rt_handle* h, const rt_rom_model* model, const double* m
 int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B,
                              int64_t nt, double dt, int bdf, double* uN_last, int* info,
                              void* stream);
+
+/* ONE implicit step for a batch of B parameters with caller-supplied sampled entries -- the form the
+ * reference's own time loop needs when the assemble(mu, t, entries[, u_n]) callback stays on the host
+ * (FEniCS; rom/rom.py:486-492 with deim/deim.py:437-445 inside every assemble_* call):
+ *   F      : B x Qsum row-major, Qsum = sum of ops[i].m; row b = the sampled entries f_local of every
+ *            reductor side by side in model order (an operator with m == 0 is absent and skipped);
+ *   theta_i = PT_U_i^-1 f_i ;  M = sum theta_mass A_q ;  K = bdf M + dt sum_(other matrix ops) ;
+ *   b = M w + dt f_rhs  with w = u_n (bdf 1) or 2 u_n - 0.5 u_nm1 (bdf 2, rom/rom.py:919-925) ;  K u = b.
+ *   bdf coefficient: 1.5 when bdf == 2 and step > 0, else 1.0 (rom/rom.py:481-483).
+ * Optional dense terms for operators WITHOUT a reductor, projected by the caller (rom/rom.py:135-158):
+ *   K += Kadd[b], M += Madd[b] (B x N x N row-major), b += fadd[b] (B x N); pass NULL when unused.
+ *   (Kadd must already contain bdf * Madd + dt * (...): it is added to K as is.)
+ * State (device, caller-owned, B x N row-major): Unm1 <- Un, Un <- solution (rom/rom.py:499-503).
+ * model->ops[i].C / .T / model->evaluator are not read.  info: B ints, zero-initialised by the caller
+ * before the first step; set to step+1 where a zero pivot was met. */
+int rt_online_step_f64(rt_handle* h, const rt_rom_model* model, const double* F, int64_t B, double dt,
+                       int bdf, int64_t step, const double* Kadd, const double* Madd,
+                       const double* fadd, double* Un, double* Unm1, int* info, void* stream);
 
 /* Host-only helper (no device work): parameters per chunk the sweep uses for a batch of B parameters,
  * reduced dimension N, on a device with sm_count SMs -- a multiple of 128 chosen so that the assembly

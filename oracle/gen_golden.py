@@ -256,6 +256,124 @@ def gen_solve():
     print("solve:", names, {k: v.shape for k, v in out.items() if "bdf" in k})
 
 
+def _walk_params(ts, **kw):
+    base = {"ts": ts, "num_snapshots": None}
+    base.update(kw)
+    return base
+
+
+def gen_treewalk():
+    """Offline stage through the reference's own run(): two-/three-level POD tree walk, greedy mesh,
+    projection and online evaluation, on the FEniCS-free problems of oracle/synthetic_problems.py."""
+    from romtime.deim.deim import DiscreteEmpiricalInterpolation
+    from romtime.deim.mdeim import MatrixDiscreteEmpiricalInterpolation
+    from romtime.deim.nonlinear import MatrixDiscreteEmpiricalInterpolationNonlinear
+    from romtime.rom.rom import RomConstructorNonlinear
+    import synthetic_problems as sprob
+
+    out = {}
+    ts = [float(t) for t in np.linspace(0.05, 1.0, 12)]
+    space = sprob.mu_space(5, seed=41)
+    online = sprob.mu_space(3, seed=42)
+    ts_online = [0.11, 0.52, 0.93]
+    rng = np.random.default_rng(15)
+
+    # ---- DEIM: fixed sizes, then tolerances (ragged time-basis widths)
+    vp = sprob.VectorProblem()
+    V = np.linalg.qr(rng.standard_normal((vp.Nh, 6)))[0]
+    out["V_vec"] = V
+    for tag, params in (("deim_num", _walk_params(ts, num_mu=7, num_time=5)),
+                        ("deim_tol", _walk_params(ts, tol_mu=1.0 - 1e-9, tol_time=1.0 - 1e-7))):
+        d = DiscreteEmpiricalInterpolation(assemble=vp.assemble, name=tag, tree_walk_params=params)
+        d.setup(rnd=0)
+        d.run(mu_space=[dict(m) for m in space])
+        d.project_basis(V)
+        d.evaluate(ts=ts_online, mu_space=[dict(m) for m in online])
+        out[f"{tag}/basis_fom"] = d.basis_fom
+        out[f"{tag}/sigmas"] = d.sigmas
+        out[f"{tag}/dofs"] = np.array([e[0] for e in d.dofs], dtype=np.int64)
+        out[f"{tag}/PT_U"] = d.PT_U
+        out[f"{tag}/basis_rom"] = d.basis_rom
+        out[f"{tag}/widths_time"] = np.array([d.report["offline"]["basis-shape-time"][i] for i in range(len(space))])
+        out[f"{tag}/width_after_walk"] = np.array(d.report["offline"]["basis-shape-after-tree-walk"])
+        out[f"{tag}/errors"] = np.array([d.errors_rom[i] for i in range(len(online))])
+        out[f"{tag}/interp_fom"] = d.interpolate(online[0], 0.37, which="fom")
+        out[f"{tag}/interp_rom"] = d.interpolate(online[0], 0.37, which="rom")
+
+    # ---- MDEIM
+    mp = sprob.MatrixProblem()
+    Vm = np.linalg.qr(rng.standard_normal((mp.Nh, 5)))[0]
+    out["V_mat"] = Vm
+    md = MatrixDiscreteEmpiricalInterpolation(assemble=mp.assemble, name="mdeim", tree_walk_params=_walk_params(ts, num_mu=8, num_time=5))
+    md.grid = None
+    from romtime.rom.base import Reductor
+    Reductor.setup(md, rnd=0)
+    md.rows, md.cols = md.get_matrix_topology(mu=space[0], t=1.0)
+    md.run(mu_space=[dict(m) for m in space])
+    md.project_basis(Vm)
+    md.evaluate(ts=ts_online, mu_space=[dict(m) for m in online])
+    out["mdeim/rows"] = np.array(md.rows, dtype=np.int64)
+    out["mdeim/cols"] = np.array(md.cols, dtype=np.int64)
+    out["mdeim/basis_fom"] = md.basis_fom
+    out["mdeim/sigmas"] = md.sigmas
+    out["mdeim/dofs_rc"] = np.array(md.dofs, dtype=np.int64)
+    out["mdeim/PT_U"] = md.PT_U
+    out["mdeim/basis_rom"] = md.basis_rom
+    out["mdeim/errors"] = np.array([md.errors_rom[i] for i in range(len(online))])
+    out["mdeim/interp_rom"] = md.interpolate(online[1], 0.41, which="rom")
+    out["mdeim/interp_fom_data"] = md.interpolate(online[1], 0.41, which="fom").toarray()
+
+    # ---- N-MDEIM (three-level walk) + truncate
+    npb = sprob.NonlinearMatrixProblem()
+    psi = npb.state_basis(3)
+    nm = MatrixDiscreteEmpiricalInterpolationNonlinear(assemble=npb.assemble, name="nmdeim",
+                                                       tree_walk_params=_walk_params(ts[:6], num_mu=9, num_time=6))
+    Reductor.setup(nm, rnd=0)
+    nm.rows, nm.cols = nm.get_matrix_topology(mu=space[0], t=1.0, u_n=psi[:, 0])
+    nm.run(u_n=psi, mu_space=[dict(m) for m in space[:3]])
+    nm.project_basis(Vm)
+    u_probe = 0.2 + 0.1 * np.cos(2 * np.pi * npb.x)
+    out["nmdeim/psi"] = psi
+    out["nmdeim/u_probe"] = u_probe
+    out["nmdeim/rows"] = np.array(nm.rows, dtype=np.int64)
+    out["nmdeim/cols"] = np.array(nm.cols, dtype=np.int64)
+    out["nmdeim/basis_fom"] = nm.basis_fom
+    out["nmdeim/sigmas"] = nm.sigmas
+    out["nmdeim/dofs_rc"] = np.array(nm.dofs, dtype=np.int64)
+    out["nmdeim/basis_rom"] = nm.basis_rom
+    out["nmdeim/interp_rom"] = nm.interpolate(online[2], 0.3, u_n=u_probe, which="rom")
+    tr = nm.truncate(2)
+    out["nmdeim/trunc_dofs_rc"] = np.array(tr.dofs, dtype=np.int64)
+    out["nmdeim/trunc_PT_U"] = tr.PT_U
+
+    # ---- solution reduced basis (RomConstructor.build_reduced_basis)
+    fom = sprob.SnapshotFom()
+    rom = RomConstructorNonlinear(fom=fom, grid=None, name="rb")
+    rom.setup(rnd=0)
+    import io, contextlib
+    with contextlib.redirect_stdout(io.StringIO()):
+        sols = rom.build_reduced_basis(mu_space=[dict(m) for m in space], num_basis=7,
+                                       tolerances={"tol_time": 1.0 - 1e-10})
+    out["rb/basis"] = rom.basis
+    out["rb/basis_nonlinear"] = rom.basis_nonlinear
+    out["rb/sigmas_mu"] = rom.report["offline"]["spectrum-mu"]
+    out["rb/energy_mu"] = rom.report["offline"]["energy-mu"]
+    out["rb/widths_time"] = np.array([rom.report["offline"]["basis-shape-time"][i] for i in range(len(space))])
+    out["rb/width_after_walk"] = np.array(rom.report["offline"]["basis-shape-after-tree-walk"])
+    out["rb/fom_solution_0"] = sols[0]
+    uh = fom.field(space[1], 0.3)
+    out["rb/uh"] = uh
+    out["rb/to_rom_vector"] = rom.basis.T.dot(uh)
+    out["rb/to_fom_vector"] = rom.to_fom_vector(rom.basis.T.dot(uh))
+    A = mp.matrix(space[0], 0.5)
+    from romtime.utils import project_csr
+    Vrb = np.linalg.qr(rng.standard_normal((mp.Nh, 4)))[0]
+    out["rb/V_small"] = Vrb
+    out["rb/project_csr"] = project_csr(A, Vrb)
+    np.savez_compressed(os.path.join(GOLD, "treewalk.npz"), **out)
+    print("treewalk:", {k: v.shape for k, v in out.items() if k.endswith("basis_fom") or k.endswith("basis")})
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     ref_harness.load_reference()
@@ -263,5 +381,6 @@ if __name__ == "__main__":
     gen_greedy()
     gen_project_interp()
     gen_solve()
+    gen_treewalk()
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))

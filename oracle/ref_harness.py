@@ -62,6 +62,9 @@ def load_reference():
     sys.modules["dolfin.cpp"].la = sys.modules["dolfin.cpp.la"]
     sys.modules["dolfin"].cpp = sys.modules["dolfin.cpp"]
     sys.modules["fenics"].DOLFIN_EPS = 3e-16
+    # utils.bilinear_to_csr (utils.py:75-93) goes fenics.as_backend_type(matrix).mat().getValuesCSR():
+    # synthetic_problems.PetscLikeMatrix answers that protocol for scipy matrices, so MDEIM.run works unmodified.
+    sys.modules["fenics"].as_backend_type = lambda matrix: matrix
     _stub("matplotlib.pyplot")
     sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
     sys.modules["seaborn"].set_theme = lambda *a, **k: None

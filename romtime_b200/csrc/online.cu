@@ -117,6 +117,9 @@ struct SweepPlan {
     int Qmat, Qall;             // rows of the 5 matrix operators / all six (multiples of 16)
     int evaluator;
     int Bc, Bcpad;              // parameters in this chunk / padded row stride of q-major buffers
+    int ldu;                    // row stride of the state vectors Un / Unm1 (Npad internally, N for caller-owned state)
+    int qsum;                   // sum of the unpadded m[i] (row length of caller-supplied sampled entries)
+    int msum[kNOps + 1];        // prefix sums of m[i]
 };
 
 // phi(mu, t): problems/piston.py:18-60 ("rest" / "sudden"), fom/nonlinear.py:159-166 (b0),
@@ -145,16 +148,38 @@ __global__ void k_state(SweepPlan pl, const double* __restrict__ mu, double t, i
                         const double* __restrict__ Un, const double* __restrict__ Unm1, double* __restrict__ Phi,
                         double* __restrict__ Ustar, double* __restrict__ Wv) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e < pl.Bc) {
+    if (mu && e < pl.Bc) {
         double phi[RT_NF];
         piston_features(pl.evaluator, mu[e * 3 + 0], mu[e * 3 + 1], mu[e * 3 + 2], t, phi);
 #pragma unroll
         for (int f = 0; f < RT_NF; ++f) Phi[(int64_t)f * pl.Bcpad + e] = phi[f];
     }
     if (e < (int64_t)pl.Bc * pl.Npad) {
-        const double un = Un[e], um = Unm1[e];
+        const int64_t p = e / pl.Npad;
+        const int j = (int)(e - p * pl.Npad);
+        const double un = j < pl.N ? Un[p * pl.ldu + j] : 0.0, um = j < pl.N ? Unm1[p * pl.ldu + j] : 0.0;
         Ustar[e] = have_prev ? 2.0 * un - um : un;
         Wv[e] = bdf2 ? 2.0 * un - 0.5 * um : un;
+    }
+}
+
+// Caller-supplied sampled entries (rt_online_step_f64): Fext[p][msum[op] + k] -> F[qoff[op] + k][p], scaled
+// like k_entries (mass unscaled, everything else times dt); padding rows are zero.
+__global__ void __launch_bounds__(256) k_entries_ext(SweepPlan pl, const double* __restrict__ Fext, double dt,
+                                                     double* __restrict__ F) {
+    const int p = blockIdx.x * 256 + threadIdx.x;
+    if (p >= pl.Bc) return;
+    const int q0 = blockIdx.y * 32;
+    for (int q = q0; q < q0 + 32 && q < pl.Qall; ++q) {
+        int op = 0;
+        while (q >= pl.qoff[op + 1]) ++op;
+        const int k = q - pl.qoff[op];
+        double v = 0.0;
+        if (k < pl.m[op]) {
+            v = Fext[(int64_t)p * pl.qsum + pl.msum[op] + k];
+            if (op != 0) v *= dt;
+        }
+        F[(int64_t)q * pl.Bcpad + p] = v;
     }
 }
 
@@ -187,10 +212,18 @@ __global__ void __launch_bounds__(256) k_entries(SweepPlan pl, const double* __r
 // (rom.py:499-503) and writes the reduced solution (rom.py:537-549 "rom" storage).
 constexpr int kLuThreads = 256;
 
+// Optional dense additive terms of rt_online_step_f64 (operators without a hyper-reductor, projected by
+// the caller): K += Kadd[p], M += Madd[p] (both N x N row-major per parameter), b += fadd[p] (N).
+struct LuExtras {
+    const double* Kadd;
+    const double* Madd;
+    const double* fadd;
+};
+
 template <int R>
 __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const double* __restrict__ Kmat,
                                                         const double* __restrict__ Mmat, const double* __restrict__ From,
-                                                        const double* __restrict__ Wv, double* __restrict__ Un,
+                                                        const double* __restrict__ Wv, LuExtras ex, double* __restrict__ Un,
                                                         double* __restrict__ Unm1, double* __restrict__ uN_out,
                                                         int64_t out_stride_p, int64_t out_off, int* __restrict__ info,
                                                         int step) {
@@ -205,16 +238,18 @@ __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const dou
     const int64_t p = blockIdx.x;
     const double* Kp = Kmat + p * pl.ldk;
     const double* Mp = Mmat + p * pl.ldk;
-    for (int e = tid; e < N * N; e += kLuThreads) a[(e / N) * ld + (e % N)] = Kp[e];
+    const double* Ka = ex.Kadd ? ex.Kadd + p * N * N : nullptr;
+    const double* Ma = ex.Madd ? ex.Madd + p * N * N : nullptr;
+    for (int e = tid; e < N * N; e += kLuThreads) a[(e / N) * ld + (e % N)] = Kp[e] + (Ka ? Ka[e] : 0.0);
     if (tid < N) wv[tid] = Wv[p * pl.Npad + tid];
     if (tid == 0) singular = 0;
     __syncthreads();
     for (int i = warp; i < N; i += kLuThreads / 32) {
         double dot = 0.0;
-        for (int j = lane; j < N; j += 32) dot = fma(Mp[i * N + j], wv[j], dot);
+        for (int j = lane; j < N; j += 32) dot = fma(Mp[i * N + j] + (Ma ? Ma[i * N + j] : 0.0), wv[j], dot);
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
-        if (lane == 0) a[i * ld + N] = dot + From[p * pl.Npad + i];
+        if (lane == 0) a[i * ld + N] = dot + From[p * pl.Npad + i] + (ex.fadd ? ex.fadd[p * N + i] : 0.0);
     }
     __syncthreads();
     const int ty = tid >> 5, tx = lane;
@@ -271,7 +306,7 @@ __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const dou
         for (int r = 0; r < R; ++r) {
             const int e = r * 32 + lane;
             if (e < N) {
-                const int64_t s = p * pl.Npad + e;
+                const int64_t s = p * pl.ldu + e;
                 Unm1[s] = Un[s];
                 Un[s] = bv[r];
                 if (uN_out) uN_out[p * out_stride_p + out_off + e] = bv[r];
@@ -292,7 +327,8 @@ __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const dou
 // coalesced staging of an N x N row-major matrix into padded shared memory: warp w takes rows w, w+NW, ...;
 // 16 rows (32 loads per lane) are issued before the first store so that one round trip covers them
 template <int NW, int LD>
-__device__ __forceinline__ void stage_matrix(double* __restrict__ stage, const double* __restrict__ src, int N, int warp, int lane) {
+__device__ __forceinline__ void stage_matrix(double* __restrict__ stage, const double* __restrict__ src,
+                                             const double* __restrict__ add, int N, int warp, int lane) {
     for (int i0 = warp; i0 < N; i0 += 16 * NW) {
         double v0[16], v1[16];
 #pragma unroll
@@ -301,12 +337,18 @@ __device__ __forceinline__ void stage_matrix(double* __restrict__ stage, const d
             v0[u] = (i < N && lane < N) ? __ldg(src + i * N + lane) : 0.0;
             v1[u] = (i < N && lane + 32 < N) ? __ldg(src + i * N + lane + 32) : 0.0;
         }
+
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
             const int i = i0 + u * NW;
             if (i < N && lane < N) stage[i * LD + lane] = v0[u];
             if (i < N && lane + 32 < N) stage[i * LD + lane + 32] = v1[u];
         }
+    }
+    if (add) {  // rt_online_step_f64 only: dense additive term, each warp revisits the rows it staged
+        __syncwarp();
+        for (int i = warp; i < N; i += NW)
+            for (int j = lane; j < N; j += 32) stage[i * LD + j] += __ldg(add + i * N + j);
     }
 }
 
@@ -369,7 +411,7 @@ template <int NP>
 __global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl, const double* __restrict__ Kmat,
                                                                  const double* __restrict__ Mmat,
                                                                  const double* __restrict__ From, const double* __restrict__ Wv,
-                                                                 double* __restrict__ Un, double* __restrict__ Unm1,
+                                                                 LuExtras ex, double* __restrict__ Un, double* __restrict__ Unm1,
                                                                  double* __restrict__ uN_out, int64_t out_stride_p,
                                                                  int64_t out_off, int* __restrict__ info, int step) {
     constexpr int LD = NP + 1;
@@ -387,7 +429,7 @@ __global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl,
     const double* Kp = Kmat + p * pl.ldk;
     const double* Mp = Mmat + p * pl.ldk;
 
-    stage_matrix<NW, LD>(stage, Mp, N, warp, lane);
+    stage_matrix<NW, LD>(stage, Mp, ex.Madd ? ex.Madd + p * N * N : nullptr, N, warp, lane);
     wv[t] = t < N ? Wv[p * pl.Npad + t] : 0.0;
     __syncthreads();
     double bt = 0.0;
@@ -397,9 +439,10 @@ __global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl,
         for (; j + 1 < N; j += 2) { b0 = fma(stage[t * LD + j], wv[j], b0); b1 = fma(stage[t * LD + j + 1], wv[j + 1], b1); }
         if (j < N) b0 = fma(stage[t * LD + j], wv[j], b0);
         bt = (b0 + b1) + From[p * pl.Npad + t];
+        if (ex.fadd) bt += ex.fadd[p * N + t];
     }
     __syncthreads();
-    stage_matrix<NW, LD>(stage, Kp, N, warp, lane);
+    stage_matrix<NW, LD>(stage, Kp, ex.Kadd ? ex.Kadd + p * N * N : nullptr, N, warp, lane);
     __syncthreads();
     double r[NP + 1];
 #pragma unroll
@@ -440,7 +483,7 @@ __global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl,
         for (int q = 0; q < NW; ++q) {
             const int e = q * 32 + lane;
             if (e < N) {
-                const int64_t s = p * pl.Npad + e;
+                const int64_t s = p * pl.ldu + e;
                 Unm1[s] = Un[s];
                 Un[s] = xv[q];
                 if (uN_out) uN_out[p * out_stride_p + out_off + e] = xv[q];
@@ -566,9 +609,16 @@ size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
     return setup_end;
 }
 
+struct StepOut {
+    double* uN_out;        // nullable
+    int64_t stride_p, off;
+    int* info;
+    int step;
+};
+
 template <int R>
-int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* uN_out, int64_t out_stride_p,
-              int64_t out_off, int* info, int step, cudaStream_t st) {
+int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o,
+              cudaStream_t st) {
     const int ld = (pl.N + 1) | 1;
     const size_t smem = ((size_t)pl.N * ld + 2 * pl.N) * sizeof(double);
     static bool attr_set[8] = {false};
@@ -576,61 +626,77 @@ int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* 
         RT_CUDA(h, cudaFuncSetAttribute(k_lu_solve<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
         attr_set[R] = true;
     }
-    k_lu_solve<R><<<pl.Bc, kLuThreads, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, b.Un, b.Unm1, uN_out, out_stride_p,
-                                                   out_off, info, step);
+    k_lu_solve<R><<<pl.Bc, kLuThreads, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
+                                                   o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
 
 template <int NP>
-int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, double* uN_out, int64_t out_stride_p,
-                  int64_t out_off, int* info, int step, cudaStream_t st) {
+int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o,
+                  cudaStream_t st) {
     const size_t smem = ((size_t)NP * (NP + 1) + 2 * (NP / 32) * (NP + 2) + 2 * NP) * sizeof(double) + 16;
     static bool attr_set = false;
     if (!attr_set) {
         RT_CUDA(h, cudaFuncSetAttribute(k_lu_reg<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         attr_set = true;
     }
-    k_lu_reg<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, b.Un, b.Unm1, uN_out, out_stride_p, out_off,
-                                          info, step);
+    k_lu_reg<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off, o.info,
+                                          o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
 
-int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, double dt, int bdf,
-               double* uN_out, double* uN_last, int* info, cudaStream_t st) {
-    RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1);
-    RT_REQUIRE(h, bdf == 1 || bdf == 2);
+// Everything that is fixed for one model and one maximum chunk size: the plan, the carved scratch and the
+// concatenated zero-padded operator tables.
+struct SweepCtx {
+    SweepPlan pl;
+    SweepBuffers b;
+    bool has_T;
+    int64_t chunk;
+};
+
+int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_evaluator, cudaStream_t st, SweepCtx& cx) {
     RT_REQUIRE(h, model->n_ops == kNOps);
     RT_REQUIRE(h, model->N >= 1 && model->N <= 128);
     RT_REQUIRE(h, model->evaluator == 0 || model->evaluator == 1);
-    SweepPlan pl;
+    SweepPlan& pl = cx.pl;
+    SweepBuffers& b = cx.b;
     memset(&pl, 0, sizeof(pl));
     pl.N = model->N;
     pl.Npad = (int)even64(pl.N);
+    pl.ldu = pl.Npad;
     pl.N2 = pl.N * pl.N;
     pl.ldk = (int)even64(pl.N2);
     pl.evaluator = model->evaluator;
-    int off = 0;
+    int off = 0, msum = 0;
     for (int i = 0; i < kNOps; ++i) {
         const rt_rom_operator& op = model->ops[i];
-        RT_REQUIRE(h, op.m >= 1 && op.basis_rom && op.PT_Uinv && op.C);
-        RT_REQUIRE(h, (i == kRhs) == (op.is_vector != 0));
-        RT_REQUIRE(h, op.ld >= (i == kRhs ? pl.N : pl.N2));
+        RT_REQUIRE(h, op.m >= 0);  // m == 0: operator absent (e.g. no convection for a fixed-domain ROM)
+        if (op.m > 0) {
+            RT_REQUIRE(h, op.basis_rom && op.PT_Uinv);
+            RT_REQUIRE(h, !need_evaluator || op.C);
+            RT_REQUIRE(h, (i == kRhs) == (op.is_vector != 0));
+            RT_REQUIRE(h, op.ld >= (i == kRhs ? pl.N : pl.N2));
+        }
         pl.m[i] = op.m;
         pl.mpad[i] = (int)pad16(op.m);
         pl.qoff[i] = off;
+        pl.msum[i] = msum;
         off += pl.mpad[i];
+        msum += op.m;
     }
     pl.qoff[kNOps] = off;
+    pl.msum[kNOps] = msum;
+    pl.qsum = msum;
     pl.Qall = off;
     pl.Qmat = pl.qoff[kRhs];
-    const int64_t chunk = plan_chunk(B, (pl.N2 + dg::BN - 1) / dg::BN, h->sm_count);
-    const int64_t Bc_max = B < chunk ? B : chunk;
+    RT_REQUIRE(h, pl.Qall >= 1);
+    cx.chunk = plan_chunk(B, (pl.N2 + dg::BN - 1) / dg::BN, h->sm_count);
+    const int64_t Bc_max = B < cx.chunk ? B : cx.chunk;
     pl.Bcpad = (int)(ceil_div64(Bc_max, 128) * 128);
     pl.Bc = (int)Bc_max;
 
-    SweepBuffers b;
     Carver sizing{nullptr};
     carve(sizing, pl, b);
     void* ws;
@@ -643,6 +709,7 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
     RT_CUDA(h, cudaMemsetAsync(ws, 0, setup_bytes, st));
     for (int i = 0; i < kNOps; ++i) {
         const rt_rom_operator& op = model->ops[i];
+        if (op.m == 0) continue;
         const int q0 = pl.qoff[i];
         if (i != kRhs)
             RT_CUDA(h, cudaMemcpy2DAsync(b.basis_cat + (size_t)q0 * pl.ldk, (size_t)pl.ldk * 8, op.basis_rom, (size_t)op.ld * 8,
@@ -650,12 +717,13 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
         else
             RT_CUDA(h, cudaMemcpy2DAsync(b.basis_rhs, (size_t)pl.Npad * 8, op.basis_rom, (size_t)op.ld * 8, (size_t)pl.N * 8,
                                          op.m, cudaMemcpyDeviceToDevice, st));
-        RT_CUDA(h, cudaMemcpyAsync(b.Ccat + (size_t)q0 * RT_NF, op.C, (size_t)op.m * RT_NF * 8, cudaMemcpyDeviceToDevice, st));
+        if (op.C)
+            RT_CUDA(h, cudaMemcpyAsync(b.Ccat + (size_t)q0 * RT_NF, op.C, (size_t)op.m * RT_NF * 8, cudaMemcpyDeviceToDevice, st));
         RT_CUDA(h, cudaMemcpy2DAsync(b.Invcat + (size_t)q0 * pl.Qall + q0, (size_t)pl.Qall * 8, op.PT_Uinv, (size_t)op.m * 8,
                                      (size_t)op.m * 8, op.m, cudaMemcpyDeviceToDevice, st));
     }
-    const bool has_T = model->ops[kTril].T != nullptr;
-    if (has_T)
+    cx.has_T = need_evaluator && model->ops[kTril].m > 0 && model->ops[kTril].T != nullptr;
+    if (cx.has_T)
         RT_CUDA(h, cudaMemcpy2DAsync(b.Tpad, (size_t)pl.Npad * 8, model->ops[kTril].T, (size_t)pl.N * 8, (size_t)pl.N * 8,
                                      model->ops[kTril].m, cudaMemcpyDeviceToDevice, st));
     {
@@ -677,11 +745,112 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
         RT_CUDA(h, cudaMemcpyAsync(b.kt_ranges, host_ranges, tiles * sizeof(int2), cudaMemcpyHostToDevice, st));
         RT_CUDA(h, cudaStreamSynchronize(st));  // host_ranges is on the stack
     }
-    RT_CUDA(h, cudaMemsetAsync(info, 0, (size_t)B * sizeof(int), st));
+    return RT_OK;
+}
 
+// One implicit step for the current chunk (pl.Bc parameters; state in b.Un / b.Unm1 with stride pl.ldu).
+//   Fext == nullptr: sampled entries from the device evaluator (mu_c, t);
+//   Fext != nullptr: caller-supplied sampled entries (Bc x qsum row-major).
+int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fext, double t, double dt, int bdf, int64_t n,
+               const LuExtras& ex, const StepOut& o, bool profiled, cudaStream_t st) {
+    const SweepPlan& pl = cx.pl;
+    const SweepBuffers& b = cx.b;
+    int rc;
+    const int have_prev = (bdf == 2 && n > 0) ? 1 : 0;
+    const double bdfc = have_prev ? 1.5 : 1.0;  // first step uses bdf = 1.0 (rom.py:481-483)
+    const int64_t nstate = (int64_t)pl.Bc * pl.Npad;
+    Profile* prof = (Profile*)h->profile;
+    const bool pa = prof && prof->on && profiled;
+    {
+        ProfScope ps(prof, pa, 0, st);
+        k_state<<<(unsigned)ceil_div64(nstate, 256), 256, 0, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Phi, b.Ustar,
+                                                                   b.Wv);
+    }
+    RT_LAUNCH_CHECK(h);
+    const dim3 egrid((unsigned)ceil_div64(pl.Bc, 256), (unsigned)ceil_div64(pl.Qall, 32));
+    if (Fext) {
+        ProfScope ps(prof, pa, 2, st);
+        k_entries_ext<<<egrid, 256, 0, st>>>(pl, Fext, dt, b.F);
+        RT_LAUNCH_CHECK(h);
+    } else {
+        if (cx.has_T) {
+            ProfScope ps(prof, pa, 1, st);
+            dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
+            dg::Params p = dg::default_params();
+            p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
+            rc = dg::launch(h, oa, ob, p, st);
+            if (rc) return rc;
+        }
+        ProfScope ps(prof, pa, 2, st);
+        k_entries<<<egrid, 256, 0, st>>>(pl, b.Ccat, b.Phi, cx.has_T ? b.TU : nullptr, dt, b.F);
+        RT_LAUNCH_CHECK(h);
+    }
+    {   ProfScope ps(prof, pa, 3, st);  // theta = PT_U^-1 f, all reductors, block-diagonal
+        dg::Operand oa{b.Invcat, pl.Qall, pl.Qall, pl.Qall, 1}, ob{b.F, pl.Bc, pl.Qall, 1, pl.Bcpad};
+        dg::Params p = dg::default_params();
+        p.C = b.Theta; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
+        p.kt_ranges = b.kt_ranges;
+        rc = dg::launch(h, oa, ob, p, st);
+        if (rc) return rc;
+    }
+    if (pl.Qmat > 0) {
+        ProfScope ps(prof, pa, 4, st);  // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
+        dg::Operand oa{b.Theta, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
+        dg::Params p = dg::default_params();
+        p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
+        p.C2 = b.Mmat; p.hook_kt = pl.mpad[0] / 16; p.hook_scale = bdfc;
+        if (p.hook_kt >= pl.Qmat / 16) {  // only a mass reductor: K = bdf M, no k-tile left to trigger the hook
+            p.hook_kt = -1;
+            p.alpha = 1.0;
+            p.C = b.Mmat;
+            rc = dg::launch(h, oa, ob, p, st);
+            if (rc) return rc;
+            p.C = b.Kmat;
+            p.alpha = bdfc;
+        }
+        rc = dg::launch(h, oa, ob, p, st);
+        if (rc) return rc;
+    } else {
+        RT_CUDA(h, cudaMemsetAsync(b.Kmat, 0, (size_t)pl.Bc * pl.ldk * sizeof(double), st));
+        RT_CUDA(h, cudaMemsetAsync(b.Mmat, 0, (size_t)pl.Bc * pl.ldk * sizeof(double), st));
+    }
+    if (pl.m[kRhs] > 0) {
+        ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
+        dg::Operand oa{b.Theta + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
+        dg::Operand ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
+        dg::Params p = dg::default_params();
+        p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
+        rc = dg::launch(h, oa, ob, p, st);
+        if (rc) return rc;
+    } else {
+        RT_CUDA(h, cudaMemsetAsync(b.From, 0, (size_t)pl.Bc * pl.Npad * sizeof(double), st));
+    }
+    ProfScope ps_lu(prof, pa, 6, st);
     const int R = (pl.N + 31) / 32;
-    for (int64_t p0 = 0; p0 < B; p0 += chunk) {
-        pl.Bc = (int)((B - p0) < chunk ? (B - p0) : chunk);
+    if (pl.N <= 32) rc = launch_lu_reg<32>(h, pl, b, ex, o, st);
+    else if (pl.N <= 64) rc = launch_lu_reg<64>(h, pl, b, ex, o, st);
+    else switch (R) {
+        case 1: rc = launch_lu<1>(h, pl, b, ex, o, st); break;
+        case 2: rc = launch_lu<2>(h, pl, b, ex, o, st); break;
+        case 3: rc = launch_lu<3>(h, pl, b, ex, o, st); break;
+        default: rc = launch_lu<4>(h, pl, b, ex, o, st); break;
+    }
+    return rc;
+}
+
+int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, double dt, int bdf,
+               double* uN_out, double* uN_last, int* info, cudaStream_t st) {
+    RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1);
+    RT_REQUIRE(h, bdf == 1 || bdf == 2);
+    SweepCtx cx;
+    int rc = sweep_setup(h, model, B, true, st, cx);
+    if (rc) return rc;
+    SweepPlan& pl = cx.pl;
+    SweepBuffers& b = cx.b;
+    RT_CUDA(h, cudaMemsetAsync(info, 0, (size_t)B * sizeof(int), st));
+    const LuExtras none{nullptr, nullptr, nullptr};
+    for (int64_t p0 = 0; p0 < B; p0 += cx.chunk) {
+        pl.Bc = (int)((B - p0) < cx.chunk ? (B - p0) : cx.chunk);
         const size_t state_bytes = (size_t)pl.Bcpad * pl.Npad * sizeof(double);
         RT_CUDA(h, cudaMemsetAsync(b.Un, 0, state_bytes, st));    // zero initial condition (rom.py:451-452)
         RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, state_bytes, st));  // uN_n1 = zeros, not None (rom.py:456-460)
@@ -689,67 +858,10 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
         double t = 0.0;
         for (int64_t n = 0; n < nt; ++n) {
             t += dt;  // same accumulation as the reference loop (rom.py:476-479)
-            const int have_prev = (bdf == 2 && n > 0) ? 1 : 0;
-            const double bdfc = have_prev ? 1.5 : 1.0;  // first step uses bdf = 1.0 (rom.py:481-483)
-            const int64_t nstate = (int64_t)pl.Bc * pl.Npad;
-            Profile* prof = (Profile*)h->profile;
-            const bool pa = prof && prof->on && p0 == 0;
-            { ProfScope ps(prof, pa, 0, st);
-            k_state<<<(unsigned)ceil_div64(nstate, 256), 256, 0, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Phi,
-                                                                       b.Ustar, b.Wv);
-            }
-            RT_LAUNCH_CHECK(h);
-            if (has_T) {
-                ProfScope ps(prof, pa, 1, st);
-                dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
-                dg::Params p = dg::default_params();
-                p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
-                rc = dg::launch(h, oa, ob, p, st);
-                if (rc) return rc;
-            }
-            { ProfScope ps(prof, pa, 2, st);
-            k_entries<<<dim3((unsigned)ceil_div64(pl.Bc, 256), (unsigned)ceil_div64(pl.Qall, 32)), 256, 0, st>>>(
-                pl, b.Ccat, b.Phi, has_T ? b.TU : nullptr, dt, b.F);
-            }
-            RT_LAUNCH_CHECK(h);
-            {   ProfScope ps(prof, pa, 3, st);  // theta = PT_U^-1 f, all reductors, block-diagonal
-                dg::Operand oa{b.Invcat, pl.Qall, pl.Qall, pl.Qall, 1}, ob{b.F, pl.Bc, pl.Qall, 1, pl.Bcpad};
-                dg::Params p = dg::default_params();
-                p.C = b.Theta; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
-                p.kt_ranges = b.kt_ranges;
-                rc = dg::launch(h, oa, ob, p, st);
-                if (rc) return rc;
-            }
-            {   ProfScope ps(prof, pa, 4, st);  // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
-                dg::Operand oa{b.Theta, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
-                dg::Params p = dg::default_params();
-                p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
-                p.C2 = b.Mmat; p.hook_kt = pl.mpad[0] / 16; p.hook_scale = bdfc;
-                rc = dg::launch(h, oa, ob, p, st);
-                if (rc) return rc;
-            }
-            {   ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
-                dg::Operand oa{b.Theta + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
-                dg::Operand ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
-                dg::Params p = dg::default_params();
-                p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
-                rc = dg::launch(h, oa, ob, p, st);
-                if (rc) return rc;
-            }
-            double* out = nullptr;
-            int64_t ostride = 0, ooff = 0;
-            if (uN_out) { out = uN_out + p0 * nt * pl.N; ostride = nt * pl.N; ooff = n * pl.N; }
-            else if (uN_last && n == nt - 1) { out = uN_last + p0 * pl.N; ostride = pl.N; ooff = 0; }
-            int* info_c = info + p0;
-            ProfScope ps_lu(prof, pa, 6, st);
-            if (pl.N <= 32) rc = launch_lu_reg<32>(h, pl, b, out, ostride, ooff, info_c, (int)n, st);
-            else if (pl.N <= 64) rc = launch_lu_reg<64>(h, pl, b, out, ostride, ooff, info_c, (int)n, st);
-            else switch (R) {
-                case 1: rc = launch_lu<1>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
-                case 2: rc = launch_lu<2>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
-                case 3: rc = launch_lu<3>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
-                default: rc = launch_lu<4>(h, pl, b, out, ostride, ooff, info_c, (int)n, st); break;
-            }
+            StepOut o{nullptr, 0, 0, info + p0, (int)n};
+            if (uN_out) { o.uN_out = uN_out + p0 * nt * pl.N; o.stride_p = nt * pl.N; o.off = n * pl.N; }
+            else if (uN_last && n == nt - 1) { o.uN_out = uN_last + p0 * pl.N; o.stride_p = pl.N; o.off = 0; }
+            rc = sweep_step(h, cx, mu_c, nullptr, t, dt, bdf, n, none, o, p0 == 0, st);
             if (rc) return rc;
         }
     }
@@ -772,6 +884,32 @@ extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model,
     RT_REQUIRE(h, uN_last);
     RT_CUDA(h, cudaSetDevice(h->device));
     return sweep_impl(h, model, mu, B, nt, dt, bdf, nullptr, uN_last, info, rt_stream(stream));
+}
+
+extern "C" int rt_online_step_f64(rt_handle* h, const rt_rom_model* model, const double* F, int64_t B, double dt, int bdf,
+                                  int64_t step, const double* Kadd, const double* Madd, const double* fadd, double* Un,
+                                  double* Unm1, int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, model && F && Un && Unm1 && info && B >= 1 && step >= 0);
+    RT_REQUIRE(h, bdf == 1 || bdf == 2);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    SweepCtx cx;
+    int rc = sweep_setup(h, model, B, false, st, cx);
+    if (rc) return rc;
+    SweepPlan& pl = cx.pl;
+    pl.ldu = pl.N;  // caller-owned state, B x N row-major
+    const int64_t N2 = pl.N2;
+    for (int64_t p0 = 0; p0 < B; p0 += cx.chunk) {
+        pl.Bc = (int)((B - p0) < cx.chunk ? (B - p0) : cx.chunk);
+        cx.b.Un = Un + p0 * pl.N;
+        cx.b.Unm1 = Unm1 + p0 * pl.N;
+        const LuExtras ex{Kadd ? Kadd + p0 * N2 : nullptr, Madd ? Madd + p0 * N2 : nullptr, fadd ? fadd + p0 * pl.N : nullptr};
+        StepOut o{nullptr, 0, 0, info + p0, (int)step};
+        rc = sweep_step(h, cx, nullptr, F + p0 * pl.qsum, 0.0, dt, bdf, step, ex, o, false, st);
+        if (rc) return rc;
+    }
+    return RT_OK;
 }
 
 extern "C" int64_t rt_sweep_chunk(int64_t B, int N, int sm_count) {

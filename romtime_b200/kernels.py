@@ -239,40 +239,84 @@ OPS = ("mass", "stiffness", "convection", "nonlinear_lifting", "trilinear", "rhs
 
 
 class DeviceRomModel:
-    """Device-resident hyper-reduced model (rt_rom_model): per operator basis_rom (column q contiguous),
-    PT_U^-1 (computed once with rt_invert_f64), evaluator tables C (m x 12) and T (m x N)."""
+    """Device-resident hyper-reduced model (rt_rom_model).  ``model`` maps every operator name in ``OPS``
+    to ``{"basis_rom", "PT_U"[, "C", "T"]}`` or to ``None`` / nothing (operator absent, m = 0):
+    basis_rom (column q contiguous), PT_U^-1 (computed once with rt_invert_f64) and, for the device
+    evaluator of rt_online_sweep_f64, the tables C (m x 12) and T (m x N)."""
 
     def __init__(self, model, device=None):
         self.N = int(model["N"])
         self.evaluator = 0 if model.get("which", "rest") == "rest" else 1
         self._keep = []
+        self.m = []
+        self.has_evaluator = True
         self.struct = _lib.RomModel()
         self.struct.N = self.N
         self.struct.n_ops = len(OPS)
         self.struct.evaluator = self.evaluator
         for i, name in enumerate(OPS):
-            op = model[name]
+            op = model.get(name)
+            so = self.struct.ops[i]
+            so.is_vector = 1 if name == "rhs" else 0
+            if op is None:
+                so.m = 0
+                self.m.append(0)
+                continue
             basis = np.asfortranarray(np.asarray(op["basis_rom"], dtype=np.float64))  # column q contiguous
+            rows_expected = self.N if name == "rhs" else self.N * self.N
+            if basis.shape[0] != rows_expected:
+                raise ValueError(f"{name}: basis_rom has {basis.shape[0]} rows, expected {rows_expected}")
             bd = to_device(basis)
             inv = invert(np.ascontiguousarray(op["PT_U"], dtype=np.float64))
-            Cd = to_device(np.ascontiguousarray(op["C"], dtype=np.float64))
-            Td = None
+            Cd = Td = None
+            if op.get("C") is not None:
+                Cd = to_device(np.ascontiguousarray(op["C"], dtype=np.float64))
+            else:
+                self.has_evaluator = False
             if op.get("T") is not None:
                 Td = to_device(np.ascontiguousarray(op["T"], dtype=np.float64))
             self._keep += [bd, inv, Cd, Td]
-            so = self.struct.ops[i]
             so.m = basis.shape[1]
-            so.is_vector = 1 if name == "rhs" else 0
+            self.m.append(int(basis.shape[1]))
             so.basis_rom = bd.data_ptr()
-            so.ld = int(bd.stride(1))
+            so.ld = int(bd.stride(1)) if basis.shape[1] > 1 else int(basis.shape[0])
             so.PT_Uinv = inv.data_ptr()
-            so.C = Cd.data_ptr()
+            so.C = Cd.data_ptr() if Cd is not None else None
             so.T = Td.data_ptr() if Td is not None else None
+        self.qsum = sum(self.m)
+
+
+def online_step(dev_model, F, Un, Unm1, info, dt, bdf, step, Kadd=None, Madd=None, fadd=None):
+    """rt_online_step_f64: one implicit step for B parameters from caller-supplied sampled entries
+    ``F`` (B x sum(m), CUDA or NumPy).  ``Un``/``Unm1`` (B x N CUDA tensors) are updated in place."""
+    Fd = to_device(F).contiguous()
+    if Fd.dim() == 1:
+        Fd = Fd.reshape(1, -1)
+    B = Fd.shape[0]
+    if Fd.shape[1] != dev_model.qsum:
+        raise ValueError(f"sampled entries have {Fd.shape[1]} columns, the model needs {dev_model.qsum}")
+    extras = []
+    for x, shape in ((Kadd, (B, dev_model.N, dev_model.N)), (Madd, (B, dev_model.N, dev_model.N)), (fadd, (B, dev_model.N))):
+        if x is None:
+            extras.append(None)
+        else:
+            xd = to_device(x).contiguous()
+            if tuple(xd.shape) != shape:
+                raise ValueError(f"dense additive term has shape {tuple(xd.shape)}, expected {shape}")
+            extras.append(xd)
+    h = handle(Fd.device.index)
+    with torch.cuda.device(Fd.device):
+        rc = load_library().rt_online_step_f64(h, ctypes.byref(dev_model.struct), _ptr(Fd), B, float(dt), int(bdf), int(step),
+                                               _ptr(extras[0]), _ptr(extras[1]), _ptr(extras[2]), _ptr(Un), _ptr(Unm1),
+                                               _ptr(info), stream_ptr())
+    check(rc, h, "rt_online_step_f64")
 
 
 def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
     """rt_online_sweep_f64 / rt_online_sweep_last_f64.  mus: (B, 3) [a0, omega, delta].
     Returns (uN cuda tensor (B, nt, N) or (B, N), info int32 (B,))."""
+    if not dev_model.has_evaluator:
+        raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
     md = to_device(mus).contiguous()
     B = md.shape[0]
     N = dev_model.N

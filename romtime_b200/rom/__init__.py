@@ -1,0 +1,6 @@
+"""POD + reduced-order model constructors (reference rom/__init__.py)."""
+from .base import Reductor
+from .pod import orth
+from .rom import PistonEvaluator, RomConstructor, RomConstructorMoving, RomConstructorNonlinear
+
+__all__ = ["Reductor", "RomConstructor", "RomConstructorMoving", "RomConstructorNonlinear", "PistonEvaluator", "orth"]
