@@ -1,18 +1,27 @@
 // DEIM / MDEIM greedy interpolation-point selection (reference deim/deim.py:517-561).
 //
-// One persistent cooperative kernel runs the whole greedy: per step j every CTA
-//   (1) extends a bordered LU of P^T U_{:j} by the point found in step j-1 and solves for the
-//       interpolation coefficients c (warp 0, vectors in registers, LU in shared memory) --
-//       redundantly in every CTA, so no second grid barrier is needed;
-//   (2) streams its rows of U[:, :j+1] from HBM with 16-byte loads (column-major, coalesced)
-//       and forms res_i = u_j[i] - sum_k c_k U[i,k] with ONE fixed summation order (k ascending,
-//       fma) for every row, so bit-identical rows give bit-identical residuals;
-//   (3) reduces (|res|, i) with numpy.argmax semantics (first maximum, NaN is maximal) through
-//       warp shuffles -> CTA -> one grid barrier -> every CTA reduces the per-CTA slots.
-// Algorithmic HBM traffic: 8*Nh*(j+1) bytes in step j, 8*Nh*m(m+1)/2 in total, nothing written.
+// The DEIM points are the row pivots of Gaussian elimination with partial pivoting on the collateral
+// basis U (Nh x m): the residual of step j,  res_j = u_j - U_{:j} (P^T U_{:j})^-1 P^T u_j,  is column j
+// of the Schur complement.  One persistent cooperative kernel runs all m steps as a BLOCKED
+// LEFT-LOOKING elimination (block width B <= 8 columns):
 //
-// The DEIM points are the row pivots of an LU of U with partial pivoting, so the bordered LU
-// without further pivoting has |L| <= 1 (as stable as dgesv on P^T U, deim/deim.py:545-547).
+//   per block of columns J = [j0, j0+bw):
+//     (A) warp l solves  C[:, l] = (P^T U_{:j0})^-1 P^T u_{j0+l}  with the bordered LU of P^T U kept in
+//         shared memory (redundantly in every CTA: no extra grid barrier);
+//     (B) every CTA streams ITS rows of U[:, :j0+bw] from HBM once (coalesced, column-major) and forms
+//         the panel  W[:, l] = u_{j0+l} - U_{:j0} C[:, l]  in shared memory (rows are CTA-resident);
+//     (C) bw right-looking steps inside the panel, all in shared memory: arg-max of |W[:, i]| with
+//         numpy.argmax semantics (first maximum, NaN is maximal) -> per-CTA slot (value, row index and
+//         the candidate's panel row) -> ONE grid barrier -> every CTA picks the winner, eliminates
+//         W[:, l] -= W[:, i] * (W[p, l] / W[p, i]) for l > i, and warp 0 extends the bordered LU by the
+//         new point while the other warps update the panel.
+//
+// HBM traffic: 8*Nh*(j0+bw) bytes per block, 8*Nh*m*(m/B+1)/2 in total -- B times less than the unblocked
+// left-looking form (8*Nh*m(m+1)/2, what SURVEY.md 8d calls the algorithmic bytes); nothing is written.
+// Every row goes through the same fixed sequence of FMAs, so bit-identical rows (the duplicated
+// symmetric entries of an MDEIM basis) give bit-identical residuals and the lower index wins, as
+// np.argmax does in the reference.  The bordered LU needs no pivoting of its own: the points ARE the
+// GEPP pivots, so |L| <= 1 (as stable as dgesv on P^T U, deim/deim.py:545-547).
 #include <cooperative_groups.h>
 
 #include "common.cuh"
@@ -29,12 +38,16 @@ struct GreedyArgs {
     int64_t Nh;
     int64_t ld;
     int m;
-    int ldl;  // leading dimension of the LU workspace (odd -> conflict-free column access)
+    int ldl;          // leading dimension of the LU workspace (odd -> conflict-free column access)
+    int64_t rpc;      // rows per CTA (contiguous ownership)
     int64_t* dofs;
     double* PT_U;
     int* info;
     double* slot_val;   // [2][gridDim.x]
     int64_t* slot_idx;  // [2][gridDim.x]
+    double* slot_row;   // [2][gridDim.x][8]  panel row of each CTA's candidate
+    double* Wglobal;    // panel in global memory (only when it does not fit in shared memory), else null
+    int64_t ldw;        // leading dimension of the panel (rows per CTA when in shared memory)
 };
 
 __device__ __forceinline__ bool val_gt(double a, double b) {
@@ -110,155 +123,171 @@ __device__ __forceinline__ void solve_upper(const double* LU, int ldl, int n, do
     }
 }
 
-template <int R, int VEC>
+
+// ---------------------------------------------------------------------------------------------
+template <int R, int B>
 __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* LU = reinterpret_cast<double*>(smem_raw);            // m * ldl
-    double* c_s = LU + (size_t)a.m * a.ldl;                      // m
-    double* red_v = c_s + a.m;                                   // 32
-    int64_t* red_i = reinterpret_cast<int64_t*>(red_v + 32);     // 32
+    double* Cs = LU + (size_t)a.m * a.ldl;                       // m * B   coefficients of the current block
+    double* red_v = Cs + (size_t)a.m * B;                        // 32
+    double* prow_s = red_v + 32;                                 // 8       panel row of the winning point
+    int64_t* red_i = reinterpret_cast<int64_t*>(prow_s + 8);     // 32
     int64_t* dofs_s = red_i + 32;                                // m
+    double* Wsm = reinterpret_cast<double*>(dofs_s + a.m);       // B * ldw (when the panel is in shared memory)
     __shared__ int stop_s;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int m = a.m, ldl = a.ldl;
     const int64_t Nh = a.Nh, ld = a.ld;
     const double* __restrict__ U = a.U;
+    const int64_t r0 = (int64_t)blockIdx.x * a.rpc;
+    const int nrows = (int)max((int64_t)0, min(a.rpc, Nh - r0));
+    const int64_t ldw = a.ldw;
+    double* W = a.Wglobal ? a.Wglobal + r0 : Wsm;  // W[l * ldw + i_local]
     if (tid == 0) stop_s = 0;
     __syncthreads();
 
-    for (int j = 0; j < m; ++j) {
-        // ---------------- (1) bordered LU + coefficient solve (warp 0) ----------------
-        if (j > 0 && warp == 0) {
-            const int64_t p = dofs_s[j - 1];
+    for (int j0 = 0; j0 < m; j0 += B) {
+        const int bw = min(B, m - j0);
+        // ---------------- (A) coefficients of the block columns: warp l -> column j0 + l ----------------
+        if (j0 > 0 && warp < bw) {
             double v[R];
-            // new row of L:  l^T = U[p, 0:j-1] Rm^-1
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const int e = r * 32 + lane;
-                v[r] = (e < j - 1) ? U[p + (int64_t)e * ld] : 0.0;
+                v[r] = (e < j0) ? U[dofs_s[e] + (int64_t)(j0 + warp) * ld] : 0.0;
             }
-            solve_upper_T<R>(LU, ldl, j - 1, v, lane);
-            double dot = 0.0;
+            solve_unit_lower<R>(LU, ldl, j0, v, lane);  // y = L^-1 P^T u : rows 0..j0-1 of column j0+warp of Rm
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const int e = r * 32 + lane;
-                if (e < j - 1) {
-                    LU[(size_t)(j - 1) * ldl + e] = v[r];
-                    dot = fma(v[r], LU[(size_t)e * ldl + (j - 1)], dot);
-                }
+                if (e < j0) LU[(size_t)e * ldl + (j0 + warp)] = v[r];
             }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(kFull, dot, off);
-            if (lane == 0) LU[(size_t)(j - 1) * ldl + (j - 1)] = U[p + (int64_t)(j - 1) * ld] - dot;
-            __syncwarp();
-            // right-hand side b = U[dofs, j];  y = L^-1 b;  store as column j of Rm;  c = Rm^-1 y
+            solve_upper<R>(LU, ldl, j0, v, lane);       // c = Rm^-1 y   (reads LU[:j0, :j0] only)
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const int e = r * 32 + lane;
-                v[r] = (e < j) ? U[dofs_s[e] + (int64_t)j * ld] : 0.0;
-            }
-            solve_unit_lower<R>(LU, ldl, j, v, lane);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const int e = r * 32 + lane;
-                if (e < j) LU[(size_t)e * ldl + j] = v[r];
-            }
-            __syncwarp();
-            solve_upper<R>(LU, ldl, j, v, lane);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const int e = r * 32 + lane;
-                if (e < j) c_s[e] = v[r];
+                if (e < j0) Cs[(size_t)e * B + warp] = v[r];
             }
         }
+        if (j0 > 0 && bw < B)  // ragged last block: unused coefficient columns are zero
+            for (int e = tid; e < j0 * B; e += kThreads)
+                if ((e % B) >= bw) Cs[e] = 0.0;
         __syncthreads();
 
-        // ---------------- (2) stream the residual, local arg-max ----------------
-        double best_v = -1.0;
-        int64_t best_i = INT64_MAX;
-        const double* __restrict__ uj = U + (int64_t)j * ld;
-        const int64_t stride = (int64_t)gridDim.x * kThreads * VEC;
-        for (int64_t i = ((int64_t)blockIdx.x * kThreads + tid) * VEC; i < Nh; i += stride) {
-            if (VEC == 2 && i + 1 < Nh) {
-                double2 acc = *reinterpret_cast<const double2*>(uj + i);
-                const double* col = U + i;
-                int k = 0;
-                for (; k + 8 <= j; k += 8) {
-                    double2 x[8];
+        // ---------------- (B) panel  W[:, l] = u_{j0+l} - U_{:j0} C[:, l]  for this CTA's rows ----------------
+        for (int il = tid; il < nrows; il += kThreads) {
+            const double* __restrict__ row = U + r0 + il;
+            double acc[B];
 #pragma unroll
-                    for (int q = 0; q < 8; ++q)
-                        x[q] = __ldg(reinterpret_cast<const double2*>(col + (int64_t)(k + q) * ld));
+            for (int l = 0; l < B; ++l) acc[l] = (l < bw) ? row[(int64_t)(j0 + l) * ld] : 0.0;
+            int k = 0;
+            for (; k + 8 <= j0; k += 8) {
+                double x[8];
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const double ck = c_s[k + q];
-                        acc.x = fma(-ck, x[q].x, acc.x);
-                        acc.y = fma(-ck, x[q].y, acc.y);
+                for (int q = 0; q < 8; ++q) x[q] = __ldg(row + (int64_t)(k + q) * ld);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const double* c = Cs + (size_t)(k + q) * B;
+#pragma unroll
+                    for (int l = 0; l < B; ++l) acc[l] = fma(-c[l], x[q], acc[l]);
+                }
+            }
+            for (; k < j0; ++k) {
+                const double x = __ldg(row + (int64_t)k * ld);
+                const double* c = Cs + (size_t)k * B;
+#pragma unroll
+                for (int l = 0; l < B; ++l) acc[l] = fma(-c[l], x, acc[l]);
+            }
+#pragma unroll
+            for (int l = 0; l < B; ++l)
+                if (l < bw) W[(size_t)l * ldw + il] = acc[l];
+        }
+        // (each thread reads back only the panel rows it wrote itself until the CTA-level reduction below)
+
+        // ---------------- (C) bw right-looking steps inside the panel ----------------
+        for (int i = 0; i < bw; ++i) {
+            const int j = j0 + i;
+            double best_v = -1.0;
+            int64_t best_i = INT64_MAX;
+            const double* wi = W + (size_t)i * ldw;
+            for (int il = tid; il < nrows; il += kThreads) {
+                const double av = fabs(wi[il]);
+                if (val_gt(av, best_v)) { best_v = av; best_i = r0 + il; }
+            }
+            warp_arg_reduce(best_v, best_i);
+            if (lane == 0) { red_v[warp] = best_v; red_i[warp] = best_i; }
+            __syncthreads();
+            if (warp == 0) {
+                double v = red_v[lane];
+                int64_t idx = red_i[lane];
+                warp_arg_reduce(v, idx);
+                const size_t slot = (size_t)(j & 1) * gridDim.x + blockIdx.x;
+                if (lane == 0) { a.slot_val[slot] = v; a.slot_idx[slot] = idx; }
+                if (lane < 8) a.slot_row[slot * 8 + lane] = (lane < bw && idx != INT64_MAX) ? W[(size_t)lane * ldw + (idx - r0)] : 0.0;
+            }
+            grid.sync();
+            if (warp == 0) {
+                double v = -1.0;
+                int64_t idx = INT64_MAX;
+                for (unsigned s = lane; s < gridDim.x; s += 32) {
+                    const double ov = __ldcg(a.slot_val + (size_t)(j & 1) * gridDim.x + s);
+                    const int64_t oi = __ldcg(a.slot_idx + (size_t)(j & 1) * gridDim.x + s);
+                    arg_merge(v, idx, ov, oi);
+                }
+                warp_arg_reduce(v, idx);
+                const size_t owner = (size_t)(j & 1) * gridDim.x + (size_t)(idx / a.rpc);
+                double pr = 0.0;
+                if (lane < 8) { pr = __ldcg(a.slot_row + owner * 8 + lane); prow_s[lane] = pr; }
+                // row j of the bordered LU inside the block: L[j, j0+l] = W_l[p] / rho_l (l < i), Rm[j, j0+l] = W_l[p] (l >= i)
+                if (lane < bw)
+                    LU[(size_t)j * ldl + (j0 + lane)] = (lane >= i) ? pr : pr / LU[(size_t)(j0 + lane) * ldl + (j0 + lane)];
+                if (lane == 0) {
+                    dofs_s[j] = idx;
+                    if (blockIdx.x == 0) a.dofs[j] = idx;
+                    // residual identically zero: the next interpolation matrix is exactly singular
+                    // (np.linalg.solve would raise LinAlgError at deim/deim.py:547)
+                    if (v == 0.0 && j + 1 < m) {
+                        stop_s = 1;
+                        if (blockIdx.x == 0) *a.info = j + 1;
                     }
                 }
-                for (; k < j; ++k) {
-                    const double2 x = __ldg(reinterpret_cast<const double2*>(col + (int64_t)k * ld));
-                    const double ck = c_s[k];
-                    acc.x = fma(-ck, x.x, acc.x);
-                    acc.y = fma(-ck, x.y, acc.y);
-                }
-                const double a0 = fabs(acc.x), a1 = fabs(acc.y);
-                if (val_gt(a0, best_v)) { best_v = a0; best_i = i; }
-                if (val_gt(a1, best_v)) { best_v = a1; best_i = i + 1; }
-            } else {
-                // scalar path (VEC == 1, or the odd last row): same arithmetic per row
-                double acc = uj[i];
-                const double* col = U + i;
-                int k = 0;
-                for (; k + 8 <= j; k += 8) {
-                    double x[8];
+            }
+            __syncthreads();
+            if (stop_s) break;
+            if (i + 1 < bw) {
+                const double rho = prow_s[i];
+                double f[B];
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) x[q] = __ldg(col + (int64_t)(k + q) * ld);
+                for (int l = 0; l < B; ++l) f[l] = (l > i && l < bw) ? prow_s[l] / rho : 0.0;
+                for (int il = tid; il < nrows; il += kThreads) {
+                    const double wv = wi[il];
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) acc = fma(-c_s[k + q], x[q], acc);
-                }
-                for (; k < j; ++k) acc = fma(-c_s[k], __ldg(col + (int64_t)k * ld), acc);
-                const double a0 = fabs(acc);
-                if (val_gt(a0, best_v)) { best_v = a0; best_i = i; }
-            }
-        }
-        // ---------------- (3) CTA reduce -> slot -> grid barrier -> global reduce ----------------
-        warp_arg_reduce(best_v, best_i);
-        if (lane == 0) { red_v[warp] = best_v; red_i[warp] = best_i; }
-        __syncthreads();
-        if (warp == 0) {
-            double v = red_v[lane];
-            int64_t i = red_i[lane];
-            warp_arg_reduce(v, i);
-            if (lane == 0) {
-                a.slot_val[(size_t)(j & 1) * gridDim.x + blockIdx.x] = v;
-                a.slot_idx[(size_t)(j & 1) * gridDim.x + blockIdx.x] = i;
-            }
-        }
-        grid.sync();
-        if (warp == 0) {
-            double v = -1.0;
-            int64_t i = INT64_MAX;
-            for (unsigned s = lane; s < gridDim.x; s += 32) {
-                const double ov = __ldcg(a.slot_val + (size_t)(j & 1) * gridDim.x + s);
-                const int64_t oi = __ldcg(a.slot_idx + (size_t)(j & 1) * gridDim.x + s);
-                arg_merge(v, i, ov, oi);
-            }
-            warp_arg_reduce(v, i);
-            if (lane == 0) {
-                dofs_s[j] = i;
-                if (blockIdx.x == 0) a.dofs[j] = i;
-                // residual identically zero: the next interpolation matrix is exactly singular
-                // (np.linalg.solve would raise LinAlgError at deim/deim.py:547)
-                if (v == 0.0 && j + 1 < m) {
-                    stop_s = 1;
-                    if (blockIdx.x == 0) *a.info = j + 1;
+                    for (int l = 1; l < B; ++l)
+                        if (l > i && l < bw) W[(size_t)l * ldw + il] = fma(-f[l], wv, W[(size_t)l * ldw + il]);
                 }
             }
         }
-        __syncthreads();
         if (stop_s) break;
+        // ---------------- rows of L for the bw new points (columns 0..j0-1): warp i -> point j0 + i ----------------
+        if (j0 > 0 && j0 + bw < m && warp < bw) {
+            const int64_t p = dofs_s[j0 + warp];
+            double v[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int e = r * 32 + lane;
+                v[r] = (e < j0) ? U[p + (int64_t)e * ld] : 0.0;
+            }
+            solve_upper_T<R>(LU, ldl, j0, v, lane);  // l^T = U[p, :j0] Rm_{j0}^-1
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int e = r * 32 + lane;
+                if (e < j0) LU[(size_t)(j0 + warp) * ldl + e] = v[r];
+            }
+        }
+        __syncthreads();
     }
     // PT_U = U[dofs, :] (gather, exact) -- deim/deim.py:159, :212
     if (!stop_s) {
@@ -286,14 +315,28 @@ __global__ void k_to_colmajor(const double* __restrict__ src, int64_t Nh, int64_
     }
 }
 
-template <int R>
-int launch_greedy(rt_handle* h, GreedyArgs& a, bool vec2, int grid, size_t smem, cudaStream_t st) {
+size_t greedy_smem(int m, int ldl, int B, int64_t panel_ld) {
+    return ((size_t)m * ldl + (size_t)m * B + 32 + 8) * sizeof(double) + (size_t)(32 + m) * sizeof(int64_t) +
+           (size_t)B * panel_ld * sizeof(double);
+}
+
+template <int R, int B>
+int launch_greedy(rt_handle* h, GreedyArgs& a, int grid, size_t smem, cudaStream_t st) {
     void* params[] = {&a};
-    const void* fn = vec2 ? (const void*)k_deim_greedy<R, 2> : (const void*)k_deim_greedy<R, 1>;
+    const void* fn = (const void*)k_deim_greedy<R, B>;
     RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     RT_CUDA(h, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params, smem, st));
     RT_LAUNCH_CHECK(h);
     return RT_OK;
+}
+
+template <int B>
+int launch_greedy_r(rt_handle* h, GreedyArgs& a, int grid, size_t smem, cudaStream_t st) {
+    const int R = (a.m + 31) / 32;
+    if (R <= 1) return launch_greedy<1, B>(h, a, grid, smem, st);
+    if (R <= 2) return launch_greedy<2, B>(h, a, grid, smem, st);
+    if (R <= 4) return launch_greedy<4, B>(h, a, grid, smem, st);
+    return launch_greedy<5, B>(h, a, grid, smem, st);
 }
 
 }  // namespace
@@ -310,6 +353,7 @@ extern "C" int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int
     RT_CUDA(h, cudaMemsetAsync(info, 0, sizeof(int), st));
 
     GreedyArgs a;
+    memset(&a, 0, sizeof(a));
     a.Nh = Nh;
     a.m = (int)m;
     a.ldl = (int)m | 1;
@@ -334,20 +378,35 @@ extern "C" int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int
         a.U = (const double*)buf;
         a.ld = ld;
     }
-    const bool vec2 = (reinterpret_cast<uintptr_t>(a.U) % 16 == 0) && (a.ld % 2 == 0);
-    const int vec = vec2 ? 2 : 1;
-    int grid = (int)ceil_div64(Nh, (int64_t)kThreads * vec);
+    // contiguous row ownership: one CTA per SM, at least 256 rows per CTA
+    int grid = (int)ceil_div64(Nh, 256);
     if (grid > h->sm_count) grid = h->sm_count;
     if (grid < 1) grid = 1;
+    a.rpc = ceil_div64(Nh, grid);
+    grid = (int)ceil_div64(Nh, a.rpc);  // every CTA owns at least one row
+    const size_t smem_max = (size_t)h->smem_optin - 1024;
+    int B = 0;
+    if (greedy_smem(a.m, a.ldl, 8, a.rpc) <= smem_max) B = 8;
+    else if (greedy_smem(a.m, a.ldl, 4, a.rpc) <= smem_max) B = 4;
+    size_t smem;
     void* slots;
-    int rc = rt_scratch(h, 1, (size_t)grid * 2 * (sizeof(double) + sizeof(int64_t)), &slots);
+    const size_t slot_bytes = (size_t)grid * 2 * (sizeof(double) + sizeof(int64_t) + 8 * sizeof(double));
+    size_t wbytes = 0;
+    if (B == 0) {  // panel too tall for shared memory: keep it in global memory (L2-resident), 8 columns wide
+        B = 8;
+        a.ldw = (Nh + 1) & ~int64_t(1);
+        wbytes = (size_t)a.ldw * 8 * sizeof(double);
+        smem = greedy_smem(a.m, a.ldl, 8, 0);
+    } else {
+        a.ldw = a.rpc;
+        smem = greedy_smem(a.m, a.ldl, B, a.rpc);
+    }
+    int rc = rt_scratch(h, 1, slot_bytes + 256 + wbytes, &slots);
     if (rc) return rc;
     a.slot_val = (double*)slots;
-    a.slot_idx = (int64_t*)((double*)slots + 2 * (size_t)grid);
-    const size_t smem = ((size_t)a.m * a.ldl + a.m + 32) * sizeof(double) + (32 + a.m) * sizeof(int64_t);
-    const int R = (int)((m + 31) / 32);
-    if (R <= 1) return launch_greedy<1>(h, a, vec2, grid, smem, st);
-    if (R <= 2) return launch_greedy<2>(h, a, vec2, grid, smem, st);
-    if (R <= 4) return launch_greedy<4>(h, a, vec2, grid, smem, st);
-    return launch_greedy<5>(h, a, vec2, grid, smem, st);
+    a.slot_idx = (int64_t*)(a.slot_val + 2 * (size_t)grid);
+    a.slot_row = (double*)(a.slot_idx + 2 * (size_t)grid);
+    if (wbytes) a.Wglobal = (double*)(((uintptr_t)(a.slot_row + 16 * (size_t)grid) + 255) & ~uintptr_t(255));
+    if (B == 8) return launch_greedy_r<8>(h, a, grid, smem, st);
+    return launch_greedy_r<4>(h, a, grid, smem, st);
 }
