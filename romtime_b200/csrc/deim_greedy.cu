@@ -30,7 +30,7 @@ namespace cg = cooperative_groups;
 
 namespace {
 
-constexpr int kThreads = 1024;
+constexpr int kThreads = 512;  // 128 registers per thread: the slot exchange keeps 20 loads in flight per lane
 constexpr unsigned kFull = 0xffffffffu;
 
 struct GreedyArgs {
@@ -43,28 +43,101 @@ struct GreedyArgs {
     int64_t* dofs;
     double* PT_U;
     int* info;
-    double* slot_val;   // [2][gridDim.x]
-    int64_t* slot_idx;  // [2][gridDim.x]
-    double* slot_row;   // [2][gridDim.x][8]  panel row of each CTA's candidate
+    unsigned* counter;          // grid barrier counter, zeroed by the host before the launch
+    unsigned long long* slots;  // [2][gridDim.x][kSlotWords] LL words: key, row index, panel row of each CTA's candidate
     double* Wglobal;    // panel in global memory (only when it does not fit in shared memory), else null
     int64_t ldw;        // leading dimension of the panel (rows per CTA when in shared memory)
 };
 
-__device__ __forceinline__ bool val_gt(double a, double b) {
-    // numpy.argmax ordering: NaN beats everything, first occurrence is kept by the index rule
-    if (a != a) return !(b != b);
-    if (b != b) return false;
-    return a > b;
+// numpy.argmax ordering on |x| as an unsigned 64-bit key: for non-negative doubles the IEEE bit pattern is
+// monotone, NaN (canonicalised) is larger than everything, and ties go to the LOWER row index.
+constexpr unsigned long long kNanKey = 0x7ff8000000000000ull;
+__device__ __forceinline__ unsigned long long abs_key(double x) {
+    return (x != x) ? kNanKey : (unsigned long long)__double_as_longlong(fabs(x));
 }
-__device__ __forceinline__ void arg_merge(double& v, int64_t& i, double ov, int64_t oi) {
-    if (val_gt(ov, v) || (!val_gt(v, ov) && oi < i)) { v = ov; i = oi; }
+__device__ __forceinline__ void key_merge(unsigned long long& k, int64_t& i, unsigned long long ok, int64_t oi) {
+    if (ok > k || (ok == k && oi < i)) { k = ok; i = oi; }
 }
-__device__ __forceinline__ void warp_arg_reduce(double& v, int64_t& i) {
+// warp-wide (max key, then min index) with four redux.sync instead of a shuffle tree
+__device__ __forceinline__ void warp_key_reduce(unsigned long long& k, int64_t& i) {
+    const unsigned hi = (unsigned)(k >> 32), lo = (unsigned)k;
+    const unsigned mh = __reduce_max_sync(kFull, hi);
+    const unsigned ml = __reduce_max_sync(kFull, hi == mh ? lo : 0u);
+    const bool win = (hi == mh) && (lo == ml);
+    const unsigned ih = win ? (unsigned)((unsigned long long)i >> 32) : 0xffffffffu;
+    const unsigned mih = __reduce_min_sync(kFull, ih);
+    const unsigned il = (win && ih == mih) ? (unsigned)(unsigned long long)i : 0xffffffffu;
+    const unsigned mil = __reduce_min_sync(kFull, il);
+    k = ((unsigned long long)mh << 32) | ml;
+    i = (int64_t)(((unsigned long long)mih << 32) | mil);
+}
+
+// Grid-wide exchange of the per-CTA candidates without a separate barrier ("LL" protocol): every 64-bit word
+// carries 32 bits of payload and the 32-bit step number; a reader spins on the word itself until the step
+// number matches, so the data IS the flag (one L2 round trip, no fence, no atomic).  64-bit stores are
+// single-copy atomic.  The slot area is zeroed by the host before the launch and steps count from 1.
+constexpr int kSlotWords = 24;  // key (2) + idx (2) + panel row (16), padded
+__device__ __forceinline__ void ll_store(unsigned long long* p, unsigned data, unsigned step) {
+    const unsigned long long w = ((unsigned long long)data << 32) | step;
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+// grid-wide arrive / wait on a monotone counter (all CTAs are co-resident: cooperative launch).  One lane
+// per CTA polls: 148 pollers on one L2 line instead of 148 x 32 lanes spinning on the slots themselves.
+__device__ __forceinline__ void grid_arrive(unsigned* ctr) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+}
+__device__ __forceinline__ void grid_wait(const unsigned* ctr, unsigned target) {
+    unsigned v;
+    do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    } while ((int)(v - target) < 0);
+}
+
+// one 16-byte load of two LL words; returns false while either word still belongs to an older step
+__device__ __forceinline__ bool ll_try_pair(const unsigned long long* p, unsigned step, unsigned long long& out) {
+    unsigned long long w0, w1;
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+    out = (w0 & 0xffffffff00000000ull) | (w1 >> 32);
+    return ((unsigned)w0 == step) && ((unsigned)w1 == step);
+}
+
+// Warp 0 of every CTA: grid barrier, then (max key, min row index) over all CTAs' candidates and the panel
+// row of the winner (lane l < 8 returns W_l[p]).  All slot loads of a lane are in flight at once: one L2 round trip.
+__device__ __forceinline__ void grid_exchange(unsigned* counter, const unsigned long long* all, unsigned epoch, int64_t rpc,
+                                           int lane, unsigned long long& k, int64_t& idx, double& pr) {
+    __syncwarp();
+    if (lane == 0) {
+        grid_arrive(counter);
+        grid_wait(counter, epoch * gridDim.x);
+    }
+    __syncwarp();
+    constexpr int kMaxSlotsPerLane = 5;  // grid <= 160 CTAs (host clamps)
+    unsigned long long ck[kMaxSlotsPerLane], ci[kMaxSlotsPerLane];
+    bool ready;
+    do {
+        ready = true;
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        double ov = __shfl_xor_sync(kFull, v, off);
-        int64_t oi = __shfl_xor_sync(kFull, i, off);
-        arg_merge(v, i, ov, oi);
+        for (int q = 0; q < kMaxSlotsPerLane; ++q) {
+            const unsigned s = lane + 32u * q;
+            if (s < gridDim.x) {
+                const bool r0k = ll_try_pair(all + (size_t)s * kSlotWords, epoch, ck[q]);
+                const bool r1k = ll_try_pair(all + (size_t)s * kSlotWords + 2, epoch, ci[q]);
+                ready = ready && r0k && r1k;
+            }
+        }
+    } while (!ready);
+    k = 0ull;
+    idx = INT64_MAX;
+#pragma unroll
+    for (int q = 0; q < kMaxSlotsPerLane; ++q)
+        if (lane + 32u * q < gridDim.x) key_merge(k, idx, ck[q], (int64_t)ci[q]);
+    warp_key_reduce(k, idx);
+    const unsigned long long* own = all + (size_t)(idx / rpc) * kSlotWords;
+    pr = 0.0;
+    if (lane < 8) {
+        unsigned long long bits;
+        while (!ll_try_pair(own + 4 + 2 * lane, epoch, bits)) {}
+        pr = __longlong_as_double((long long)bits);
     }
 }
 
@@ -87,14 +160,14 @@ __device__ __forceinline__ void solve_unit_lower(const double* LU, int ldl, int 
     }
 }
 template <int R>
-__device__ __forceinline__ void solve_upper_T(const double* LU, int ldl, int n, double (&v)[R], int lane) {
+__device__ __forceinline__ void solve_upper_T(const double* LU, const double* rdiag, int ldl, int n, double (&v)[R], int lane) {
     // l^T Rm = v^T  <=>  Rm^T l = v  (Rm = upper part of LU incl. diagonal), forward substitution
 #pragma unroll
     for (int kr = 0; kr < R; ++kr) {
         for (int kl = 0; kl < 32; ++kl) {
             const int k = kr * 32 + kl;
             if (k >= n) break;
-            double lk = __shfl_sync(kFull, v[kr], kl) / LU[(size_t)k * ldl + k];
+            double lk = __shfl_sync(kFull, v[kr], kl) * rdiag[k];
             if (lane == kl) v[kr] = lk;
 #pragma unroll
             for (int er = kr; er < R; ++er) {
@@ -105,14 +178,14 @@ __device__ __forceinline__ void solve_upper_T(const double* LU, int ldl, int n, 
     }
 }
 template <int R>
-__device__ __forceinline__ void solve_upper(const double* LU, int ldl, int n, double (&v)[R], int lane) {
+__device__ __forceinline__ void solve_upper(const double* LU, const double* rdiag, int ldl, int n, double (&v)[R], int lane) {
     // Rm c = v, backward substitution
 #pragma unroll
     for (int kr = R - 1; kr >= 0; --kr) {
         for (int kl = 31; kl >= 0; --kl) {
             const int k = kr * 32 + kl;
             if (k >= n) continue;
-            double ck = __shfl_sync(kFull, v[kr], kl) / LU[(size_t)k * ldl + k];
+            double ck = __shfl_sync(kFull, v[kr], kl) * rdiag[k];
             if (lane == kl) v[kr] = ck;
 #pragma unroll
             for (int er = 0; er <= kr; ++er) {
@@ -127,12 +200,12 @@ __device__ __forceinline__ void solve_upper(const double* LU, int ldl, int n, do
 // ---------------------------------------------------------------------------------------------
 template <int R, int B>
 __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
-    cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+        extern __shared__ __align__(16) unsigned char smem_raw[];
     double* LU = reinterpret_cast<double*>(smem_raw);            // m * ldl
     double* Cs = LU + (size_t)a.m * a.ldl;                       // m * B   coefficients of the current block
-    double* red_v = Cs + (size_t)a.m * B;                        // 32
-    double* prow_s = red_v + 32;                                 // 8       panel row of the winning point
+    double* rdiag_s = Cs + (size_t)a.m * B;                      // m       1 / Rm[k, k]
+    unsigned long long* red_k = reinterpret_cast<unsigned long long*>(rdiag_s + a.m);  // 32
+    double* prow_s = reinterpret_cast<double*>(red_k + 32);      // 8       panel row of the winning point
     int64_t* red_i = reinterpret_cast<int64_t*>(prow_s + 8);     // 32
     int64_t* dofs_s = red_i + 32;                                // m
     double* Wsm = reinterpret_cast<double*>(dofs_s + a.m);       // B * ldw (when the panel is in shared memory)
@@ -146,6 +219,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
     const int nrows = (int)max((int64_t)0, min(a.rpc, Nh - r0));
     const int64_t ldw = a.ldw;
     double* W = a.Wglobal ? a.Wglobal + r0 : Wsm;  // W[l * ldw + i_local]
+    unsigned epoch = 0;  // grid barriers passed so far (identical in every CTA)
     if (tid == 0) stop_s = 0;
     __syncthreads();
 
@@ -165,7 +239,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
                 const int e = r * 32 + lane;
                 if (e < j0) LU[(size_t)e * ldl + (j0 + warp)] = v[r];
             }
-            solve_upper<R>(LU, ldl, j0, v, lane);       // c = Rm^-1 y   (reads LU[:j0, :j0] only)
+            solve_upper<R>(LU, rdiag_s, ldl, j0, v, lane);       // c = Rm^-1 y   (reads LU[:j0, :j0] only)
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const int e = r * 32 + lane;
@@ -210,50 +284,53 @@ __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
         // ---------------- (C) bw right-looking steps inside the panel ----------------
         for (int i = 0; i < bw; ++i) {
             const int j = j0 + i;
-            double best_v = -1.0;
+            unsigned long long best_k = 0ull;
             int64_t best_i = INT64_MAX;
             const double* wi = W + (size_t)i * ldw;
             for (int il = tid; il < nrows; il += kThreads) {
-                const double av = fabs(wi[il]);
-                if (val_gt(av, best_v)) { best_v = av; best_i = r0 + il; }
+                const unsigned long long k = abs_key(wi[il]);
+                if (k > best_k || best_i == INT64_MAX) { best_k = k; best_i = r0 + il; }
             }
-            warp_arg_reduce(best_v, best_i);
-            if (lane == 0) { red_v[warp] = best_v; red_i[warp] = best_i; }
+            warp_key_reduce(best_k, best_i);
+            if (lane == 0) { red_k[warp] = best_k; red_i[warp] = best_i; }
             __syncthreads();
             if (warp == 0) {
-                double v = red_v[lane];
-                int64_t idx = red_i[lane];
-                warp_arg_reduce(v, idx);
-                const size_t slot = (size_t)(j & 1) * gridDim.x + blockIdx.x;
-                if (lane == 0) { a.slot_val[slot] = v; a.slot_idx[slot] = idx; }
-                if (lane < 8) a.slot_row[slot * 8 + lane] = (lane < bw && idx != INT64_MAX) ? W[(size_t)lane * ldw + (idx - r0)] : 0.0;
-            }
-            grid.sync();
-            if (warp == 0) {
-                double v = -1.0;
-                int64_t idx = INT64_MAX;
-                for (unsigned s = lane; s < gridDim.x; s += 32) {
-                    const double ov = __ldcg(a.slot_val + (size_t)(j & 1) * gridDim.x + s);
-                    const int64_t oi = __ldcg(a.slot_idx + (size_t)(j & 1) * gridDim.x + s);
-                    arg_merge(v, idx, ov, oi);
+                unsigned long long k = lane < kThreads / 32 ? red_k[lane] : 0ull;
+                int64_t idx = lane < kThreads / 32 ? red_i[lane] : INT64_MAX;
+                warp_key_reduce(k, idx);
+                // ---- publish this CTA's candidate (value key, row index, its panel row) as LL words ----
+                ++epoch;
+                unsigned long long* mine = a.slots + ((size_t)(j & 1) * gridDim.x + blockIdx.x) * kSlotWords;
+                {
+                    unsigned long long payload = 0ull;
+                    if (lane < 2) payload = k;
+                    else if (lane < 4) payload = (unsigned long long)idx;
+                    else if (lane < 20) {
+                        const int l = (lane - 4) >> 1;
+                        const double wv = (l < bw && idx != INT64_MAX) ? W[(size_t)l * ldw + (idx - r0)] : 0.0;
+                        payload = (unsigned long long)__double_as_longlong(wv);
+                    }
+                    if (lane < 20) ll_store(mine + lane, (lane & 1) ? (unsigned)payload : (unsigned)(payload >> 32), epoch);
                 }
-                warp_arg_reduce(v, idx);
-                const size_t owner = (size_t)(j & 1) * gridDim.x + (size_t)(idx / a.rpc);
-                double pr = 0.0;
-                if (lane < 8) { pr = __ldcg(a.slot_row + owner * 8 + lane); prow_s[lane] = pr; }
+                double pr;
+                grid_exchange(a.counter, a.slots + (size_t)(j & 1) * gridDim.x * kSlotWords, epoch, a.rpc, lane, k, idx, pr);
+                if (lane < 8) prow_s[lane] = pr;
                 // row j of the bordered LU inside the block: L[j, j0+l] = W_l[p] / rho_l (l < i), Rm[j, j0+l] = W_l[p] (l >= i)
                 if (lane < bw)
-                    LU[(size_t)j * ldl + (j0 + lane)] = (lane >= i) ? pr : pr / LU[(size_t)(j0 + lane) * ldl + (j0 + lane)];
+                    LU[(size_t)j * ldl + (j0 + lane)] = (lane >= i) ? pr : pr * rdiag_s[j0 + lane];
+                if (lane == i) rdiag_s[j] = 1.0 / pr;
                 if (lane == 0) {
                     dofs_s[j] = idx;
                     if (blockIdx.x == 0) a.dofs[j] = idx;
                     // residual identically zero: the next interpolation matrix is exactly singular
                     // (np.linalg.solve would raise LinAlgError at deim/deim.py:547)
-                    if (v == 0.0 && j + 1 < m) {
+                    if (k == 0ull && j + 1 < m) {
                         stop_s = 1;
                         if (blockIdx.x == 0) *a.info = j + 1;
                     }
                 }
+            } else {
+                ++epoch;
             }
             __syncthreads();
             if (stop_s) break;
@@ -280,7 +357,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_deim_greedy(GreedyArgs a) {
                 const int e = r * 32 + lane;
                 v[r] = (e < j0) ? U[p + (int64_t)e * ld] : 0.0;
             }
-            solve_upper_T<R>(LU, ldl, j0, v, lane);  // l^T = U[p, :j0] Rm_{j0}^-1
+            solve_upper_T<R>(LU, rdiag_s, ldl, j0, v, lane);  // l^T = U[p, :j0] Rm_{j0}^-1
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const int e = r * 32 + lane;
@@ -316,7 +393,7 @@ __global__ void k_to_colmajor(const double* __restrict__ src, int64_t Nh, int64_
 }
 
 size_t greedy_smem(int m, int ldl, int B, int64_t panel_ld) {
-    return ((size_t)m * ldl + (size_t)m * B + 32 + 8) * sizeof(double) + (size_t)(32 + m) * sizeof(int64_t) +
+    return ((size_t)m * ldl + (size_t)m * B + m + 32 + 8) * sizeof(double) + (size_t)(32 + m) * sizeof(int64_t) +
            (size_t)B * panel_ld * sizeof(double);
 }
 
@@ -381,6 +458,7 @@ extern "C" int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int
     // contiguous row ownership: one CTA per SM, at least 256 rows per CTA
     int grid = (int)ceil_div64(Nh, 256);
     if (grid > h->sm_count) grid = h->sm_count;
+    if (grid > 160) grid = 160;  // kMaxSlotsPerLane * 32
     if (grid < 1) grid = 1;
     a.rpc = ceil_div64(Nh, grid);
     grid = (int)ceil_div64(Nh, a.rpc);  // every CTA owns at least one row
@@ -390,7 +468,7 @@ extern "C" int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int
     else if (greedy_smem(a.m, a.ldl, 4, a.rpc) <= smem_max) B = 4;
     size_t smem;
     void* slots;
-    const size_t slot_bytes = (size_t)grid * 2 * (sizeof(double) + sizeof(int64_t) + 8 * sizeof(double));
+    const size_t slot_bytes = 256 + (size_t)grid * 2 * kSlotWords * sizeof(unsigned long long);
     size_t wbytes = 0;
     if (B == 0) {  // panel too tall for shared memory: keep it in global memory (L2-resident), 8 columns wide
         B = 8;
@@ -403,10 +481,10 @@ extern "C" int rt_deim_greedy_f64(rt_handle* h, const double* U, int64_t Nh, int
     }
     int rc = rt_scratch(h, 1, slot_bytes + 256 + wbytes, &slots);
     if (rc) return rc;
-    a.slot_val = (double*)slots;
-    a.slot_idx = (int64_t*)(a.slot_val + 2 * (size_t)grid);
-    a.slot_row = (double*)(a.slot_idx + 2 * (size_t)grid);
-    if (wbytes) a.Wglobal = (double*)(((uintptr_t)(a.slot_row + 16 * (size_t)grid) + 255) & ~uintptr_t(255));
+    a.counter = (unsigned*)slots;
+    a.slots = (unsigned long long*)((char*)slots + 256);
+    RT_CUDA(h, cudaMemsetAsync(slots, 0, slot_bytes, st));  // step number 0 == "nothing published yet"
+    if (wbytes) a.Wglobal = (double*)(((uintptr_t)((char*)slots + slot_bytes) + 255) & ~uintptr_t(255));
     if (B == 8) return launch_greedy_r<8>(h, a, grid, smem, st);
     return launch_greedy_r<4>(h, a, grid, smem, st);
 }

@@ -2,7 +2,8 @@ import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from romtime_b200 import kernels
-Nh, m = 200_000, 128
+Nh = int(sys.argv[1]) if len(sys.argv) > 1 else 200_000
+m = int(sys.argv[2]) if len(sys.argv) > 2 else 128
 g = torch.Generator(device="cuda").manual_seed(1)
 A = torch.randn((m, Nh), dtype=torch.float64, device="cuda", generator=g)
 Q = torch.linalg.qr(A.T)[0]            # Nh x m (orthonormal), make column-major
