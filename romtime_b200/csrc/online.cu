@@ -493,6 +493,138 @@ __global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl,
     if (sing) atomicCAS(&info[p], 0, step + 1);
 }
 
+
+// ------------------------------------------------------------------ register-resident LU, shifting rows (N <= 64)
+// Same data layout as k_lu_reg (thread t keeps row t of [K | b] in registers) with a RUNTIME loop over the
+// elimination steps: after step k every row is shifted left by one while it is updated
+// (r[j-1] = r[j] - l * u[j]), so the pivot column is always r[0] and every register index stays static.  The
+// loop body is ~100 instructions instead of 13,000 unrolled ones (no instruction-cache misses), and per step
+//   redux.sync arg-max -> cand (8 bytes per warp) -> barrier -> the GLOBAL winner alone stores its row, once,
+//   straight into the U storage used by the back substitution -> barrier -> broadcast LDS.128 + DFMA.
+// Row k of U is stored shifted: U[k][c - k] is the entry of column c >= k, U[k][NP - k] the right-hand side.
+// First half of the steps works on NP + 1 entries per row, second half on NP / 2 + 1.
+template <int NP, int W>
+__device__ __forceinline__ void lu_shift_step(double (&r)[NP + 1], bool& done, bool& sing, int k, double* U, double* rdiag,
+                                              unsigned long long (*cand)[NP / 32], int t, int lane, int warp) {
+    constexpr int NW = NP / 32;
+    constexpr int LDU = NP + 2;
+    const int par = k & 1;
+    const double rinv = 1.0 / r[0];  // speculative: off the critical path of the arg-max
+    const unsigned long long key =
+        done ? 0ull : ((unsigned long long)__double_as_longlong(fabs(r[0])) & ~127ull) | 64ull | (unsigned long long)(63 - t);
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    if (lane == 0) cand[par][warp] = ((unsigned long long)mh << 32) | ml;
+    __syncthreads();
+    unsigned long long gk = cand[par][0];
+#pragma unroll
+    for (int w = 1; w < NW; ++w) gk = cand[par][w] > gk ? cand[par][w] : gk;
+    const int gt = 63 - (int)(gk & 63ull);
+    double* urow = U + k * LDU;
+    if (t == gt && !done) {
+#pragma unroll
+        for (int j2 = 0; j2 < W; j2 += 2) *reinterpret_cast<double2*>(urow + j2) = make_double2(r[j2], r[j2 + 1]);
+        urow[W] = r[W];
+        rdiag[k] = rinv;
+        done = true;
+        if (r[0] == 0.0) sing = true;
+    }
+    __syncthreads();
+    if (!done) {
+        const double l = r[0] * rdiag[k];
+#pragma unroll
+        for (int j2 = 0; j2 < W; j2 += 2) {
+            const double2 q = *reinterpret_cast<const double2*>(urow + j2);
+            if (j2 > 0) r[j2 - 1] = fma(-l, q.x, r[j2]);
+            r[j2] = fma(-l, q.y, r[j2 + 1]);
+        }
+        r[W - 1] = fma(-l, urow[W], r[W]);
+        r[W] = 0.0;
+    }
+}
+
+template <int NP>
+__global__ void __launch_bounds__(NP, (NP == 64 ? 5 : 8)) k_lu_shift(SweepPlan pl, const double* __restrict__ Kmat,
+                                                                   const double* __restrict__ Mmat,
+                                                                   const double* __restrict__ From, const double* __restrict__ Wv,
+                                                                   LuExtras ex, double* __restrict__ Un, double* __restrict__ Unm1,
+                                                                   double* __restrict__ uN_out, int64_t out_stride_p,
+                                                                   int64_t out_off, int* __restrict__ info, int step) {
+    constexpr int LD = NP + 1;   // staging stride (odd: conflict-free row reads)
+    constexpr int LDU = NP + 2;  // U storage stride (even: 16-byte aligned rows)
+    constexpr int NW = NP / 32;
+    extern __shared__ __align__(16) double sm[];
+    double* U = sm;                  // NP * LDU  (also the staging area for M and K)
+    double* wv = U + NP * LDU;       // NP
+    double* rdiag = wv + NP;         // NP
+    __shared__ unsigned long long cand[2][NW];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int N = pl.N;
+    const int64_t p = blockIdx.x;
+    const double* Kp = Kmat + p * pl.ldk;
+    const double* Mp = Mmat + p * pl.ldk;
+
+    stage_matrix<NW, LD>(U, Mp, ex.Madd ? ex.Madd + p * N * N : nullptr, N, warp, lane);
+    wv[t] = t < N ? Wv[p * pl.Npad + t] : 0.0;
+    __syncthreads();
+    double bt = 0.0;
+    if (t < N) {
+        double b0 = 0.0, b1 = 0.0;
+        int j = 0;
+        for (; j + 1 < N; j += 2) { b0 = fma(U[t * LD + j], wv[j], b0); b1 = fma(U[t * LD + j + 1], wv[j + 1], b1); }
+        if (j < N) b0 = fma(U[t * LD + j], wv[j], b0);
+        bt = (b0 + b1) + From[p * pl.Npad + t];
+        if (ex.fadd) bt += ex.fadd[p * N + t];
+    }
+    __syncthreads();
+    stage_matrix<NW, LD>(U, Kp, ex.Kadd ? ex.Kadd + p * N * N : nullptr, N, warp, lane);
+    __syncthreads();
+    double r[NP + 1];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) r[j] = (t < N && j < N) ? U[t * LD + j] : (j == t ? 1.0 : 0.0);
+    r[NP] = bt;
+    __syncthreads();
+
+    bool done = t >= N, sing = false;  // identity padding rows take no part
+    const int half = N < NP / 2 ? N : NP / 2;
+    for (int k = 0; k < half; ++k) lu_shift_step<NP, NP>(r, done, sing, k, U, rdiag, cand, t, lane, warp);
+    for (int k = half; k < N; ++k) lu_shift_step<NP, NP / 2>(r, done, sing, k, U, rdiag, cand, t, lane, warp);
+    __syncthreads();
+    if (warp == 0) {
+        // back substitution: x_k = (rhs_k - sum_{c > k} U[k][c - k] x_c) * rdiag[k];  rhs_k = U[k][NP - k]
+        double xv[NW];
+#pragma unroll
+        for (int q = 0; q < NW; ++q) { const int e = q * 32 + lane; xv[q] = e < N ? U[e * LDU + (NP - e)] : 0.0; }
+#pragma unroll
+        for (int kr = NW - 1; kr >= 0; --kr) {
+#pragma unroll 4
+            for (int kl = 31; kl >= 0; --kl) {
+                const int k = kr * 32 + kl;
+                if (k >= N) continue;
+                const double xk = __shfl_sync(0xffffffffu, xv[kr], kl) * rdiag[k];
+                if (lane == kl) xv[kr] = xk;
+#pragma unroll
+                for (int er = 0; er <= kr; ++er) {
+                    const int e = er * 32 + lane;
+                    if (e < k) xv[er] = fma(-U[e * LDU + (k - e)], xk, xv[er]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < NW; ++q) {
+            const int e = q * 32 + lane;
+            if (e < N) {
+                const int64_t s = p * pl.ldu + e;
+                Unm1[s] = Un[s];
+                Un[s] = xv[q];
+                if (uN_out) uN_out[p * out_stride_p + out_off + e] = xv[q];
+            }
+        }
+    }
+    if (sing) atomicCAS(&info[p], 0, step + 1);
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------ stand-alone entry points
@@ -635,14 +767,14 @@ int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const Lu
 template <int NP>
 int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o,
                   cudaStream_t st) {
-    const size_t smem = ((size_t)NP * (NP + 1) + 2 * (NP / 32) * (NP + 2) + 2 * NP) * sizeof(double) + 16;
+    const size_t smem = ((size_t)NP * (NP + 2) + 2 * NP) * sizeof(double) + 16;
     static bool attr_set = false;
     if (!attr_set) {
-        RT_CUDA(h, cudaFuncSetAttribute(k_lu_reg<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        RT_CUDA(h, cudaFuncSetAttribute(k_lu_shift<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         attr_set = true;
     }
-    k_lu_reg<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off, o.info,
-                                          o.step);
+    k_lu_shift<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
+                                            o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
