@@ -8,7 +8,7 @@ One process per GPU (``torch.distributed``, backend ``nccl`` on the box, ``gloo`
   block-wise: panels travel round a ring (``batch_isend_irecv`` double-buffered against the block GEMMs,
   NVLink 5 through the switch), rank g computes the blocks ``G[g, (g+h) % P]`` for the hops
   ``h = 0 .. P//2`` only (symmetry: the other half is the transpose, written by the same rank so the
-  assembled matrix is exactly symmetric), writes them into a zero ``n x n`` buffer and one
+  assembled matrix is exactly symmetric; the antipodal block of an even world is split between the pair), writes them into a zero ``n x n`` buffer and one
   ``all_reduce(SUM)`` of G (134 MB at n = 4096) leaves the full Gram matrix on every rank.  Every entry
   of G is produced by exactly one rank, so the reduction adds exact zeros and the result is
   bit-identical on all ranks; the eigensolve is then replicated.  The lift ``Q = sum_g S_g W_g`` is a
@@ -71,6 +71,31 @@ def _ring_exchange(send_buf, recv_buf, group):
     return dist.batch_isend_irecv(ops)
 
 
+def _cross_block(ops, G, S_local, panel, rank, src, shards, antipodal):
+    """Compute and place the Gram block of (this rank's columns) x (rank ``src``'s columns) and its transpose.
+    For an even world the antipodal pair (g, g + P/2) would both compute the same block: the LOWER rank takes the
+    first half of ITS columns against all of the partner's, the HIGHER rank all of its columns against the second
+    half of the partner's -- the two pieces tile the block exactly and the work stays balanced."""
+    lo, hi = shards[rank]
+    slo, shi = shards[src]
+    if not antipodal:
+        blk = ops.cross(S_local, panel)                     # (n_g x n_src) = S_g^T S_src
+        G[lo:hi, slo:shi] = blk
+        G[slo:shi, lo:hi] = blk.t()
+    elif rank < src:
+        h1 = (hi - lo) // 2
+        if h1 > 0:
+            blk = ops.cross(S_local[:, :h1], panel)
+            G[lo:lo + h1, slo:shi] = blk
+            G[slo:shi, lo:lo + h1] = blk.t()
+    else:
+        h1s = (shi - slo) // 2
+        if shi - slo - h1s > 0:
+            blk = ops.cross(S_local, panel[:, h1s:])
+            G[lo:hi, slo + h1s:shi] = blk
+            G[slo + h1s:shi, lo:hi] = blk.t()
+
+
 def gram_column_sharded(S_local, n, block_ops=None, group=None):
     """Raw Gram matrix ``G = S^T S`` (n x n) of the column-sharded snapshot matrix, on every rank.
 
@@ -100,13 +125,8 @@ def gram_column_sharded(S_local, n, block_ops=None, group=None):
         cur = 1 - cur
         src = (rank + h) % world
         slo, shi = shards[src]
-        # for an even world the antipodal block (h == world/2) would be computed twice: lower rank keeps it
-        if world % 2 == 0 and h == hops and rank > src:
-            continue
         panel = bufs[cur][: shi - slo].t()  # Nh x n_src view, column-major
-        blk = ops.cross(S_local, panel)     # (n_g x n_src) = S_g^T S_src
-        G[lo:hi, slo:shi] = blk
-        G[slo:shi, lo:hi] = blk.t()
+        _cross_block(ops, G, S_local, panel, rank, src, shards, world % 2 == 0 and h == hops)
     dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
     return G
 
@@ -136,12 +156,8 @@ def gram_column_sharded_overlapped(S_local, n, block_ops=None, group=None):
         reqs = _ring_exchange(bufs[cur], bufs[(h + 1) % 3], group) if h < hops else []
         src = (rank + h) % world
         slo, shi = shards[src]
-        if world % 2 == 0 and h == hops and rank > src:
-            continue
         panel = bufs[cur][: shi - slo].t()
-        blk = ops.cross(S_local, panel)
-        G[lo:hi, slo:shi] = blk
-        G[slo:shi, lo:hi] = blk.t()
+        _cross_block(ops, G, S_local, panel, rank, src, shards, world % 2 == 0 and h == hops)
     dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
     return G
 
