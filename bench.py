@@ -53,7 +53,7 @@ def workload_config(a, world):
 
 
 # ------------------------------------------------------------------------------- reference arm
-def reference_arm(a):
+def reference_arm(a, out_fd):
     """CPU arm: the oracle port of RomConstructorNonlinear.solve (the reference itself needs FEniCS and
     cannot run here) on all host cores; each step = `cores` parameters x a bounded number of time steps."""
     rank = int(os.environ.get("RANK", "0"))
@@ -82,7 +82,7 @@ def reference_arm(a):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line, out_fd)
 
 
 # ------------------------------------------------------------------------------- clocks sampler
@@ -187,10 +187,19 @@ def pod_leg(a, torch, kernels, world, rank):
 
 
 # ------------------------------------------------------------------------------- main arm
+def emit(line, fd):
+    os.write(fd, (json.dumps(line) + "\n").encode())
+
+
 def main():
     a = parse()
+    # stdout carries exactly ONE JSON line: everything libraries print while we run (NCCL banner, ...)
+    # is diverted to stderr, the line itself goes to the saved descriptor
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
-        return reference_arm(a)
+        return reference_arm(a, out_fd)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -316,7 +325,7 @@ def main():
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_baseline,
             "pod": pod, "singular_solves": bad,
         }
-        print(json.dumps(line))
+        emit(line, out_fd)
     if world > 1:
         dist.destroy_process_group()
 

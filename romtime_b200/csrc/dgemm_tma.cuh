@@ -83,6 +83,11 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
         : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
@@ -195,9 +200,20 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
     const int cw = warp - PRODUCER_WARPS;
     const int g = lane >> 2, tig = lane & 3;
     const int wm0 = (cw / WARPS_N) * (MI * 8), wn0 = (cw % WARPS_N) * (NI * 8);
-    int kk[4];
+    // Fragment addresses as 32-bit shared-space offsets (LDS with immediate offsets instead of generic 64-bit
+    // loads).  For k-step s the thread reads k index kq = 8*(tig>>1) + 2*((tig+s)&3) + (tig&1); in both majors rows
+    // mn and mn + 16 are exactly 2048 bytes apart and the swizzle term only depends on (mn & 15, k), so two base
+    // offsets per k-step (rows w0 + g and w0 + 8 + g) plus immediates cover the whole warp tile.
+    const uint32_t smem_base = smem_u32(smem);
+    uint32_t a_off[2][4], b_off[2][4];
 #pragma unroll
-    for (int s = 0; s < 4; ++s) kk[s] = 8 * (tig >> 1) + 2 * ((tig + s) & 3) + (tig & 1);
+    for (int s = 0; s < 4; ++s) {
+        const int kq = 8 * (tig >> 1) + 2 * ((tig + s) & 3) + (tig & 1);
+        a_off[0][s] = frag_off<AMAJOR>(wm0 + g, kq);
+        a_off[1][s] = frag_off<AMAJOR>(wm0 + 8 + g, kq);
+        b_off[0][s] = TILE_BYTES + frag_off<BMAJOR>(wn0 + g, kq);
+        b_off[1][s] = TILE_BYTES + frag_off<BMAJOR>(wn0 + 8 + g, kq);
+    }
 
     double acc[MI][NI][2];
     int stage = 0;
@@ -223,17 +239,14 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
                     for (int j = 0; j < NI; ++j) { acc[i][j][0] *= p.hook_scale; acc[i][j][1] *= p.hook_scale; }
             }
             mbar_wait(&full[stage], phase);
-            const unsigned char* sa = smem + stage * STAGE_BYTES;
-            const unsigned char* sb = sa + TILE_BYTES;
+            const uint32_t st_addr = smem_base + stage * STAGE_BYTES;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 double af[MI], bf[NI];
 #pragma unroll
-                for (int i = 0; i < MI; ++i)
-                    af[i] = *reinterpret_cast<const double*>(sa + frag_off<AMAJOR>(wm0 + 8 * i + g, kk[s]));
+                for (int i = 0; i < MI; ++i) af[i] = lds_f64(st_addr + a_off[i & 1][s] + (uint32_t)(i >> 1) * 2048u);
 #pragma unroll
-                for (int j = 0; j < NI; ++j)
-                    bf[j] = *reinterpret_cast<const double*>(sb + frag_off<BMAJOR>(wn0 + 8 * j + g, kk[s]));
+                for (int j = 0; j < NI; ++j) bf[j] = lds_f64(st_addr + b_off[j & 1][s] + (uint32_t)(j >> 1) * 2048u);
 #pragma unroll
                 for (int i = 0; i < MI; ++i)
 #pragma unroll
