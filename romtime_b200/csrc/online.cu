@@ -6,8 +6,9 @@
 //   k_state      : features phi(mu,t) (piston closed forms), u* and the BDF history vector w
 //   dgemm (TU)   : state-dependent part of the trilinear sampled entries  T u*
 //   k_entries    : sampled entries  f = scale * (C phi + b0 T u*)              (deim/deim.py:437-438)
-//   dgemm (theta): theta = PT_U^-1 f for all six reductors in ONE block-diagonal launch   (:491-492)
-//   dgemm (K)    : [K | M] = Theta^T Basis -- sum_q theta_q A_q^r for 5 operators, K = bdf M + dt(...)
+//   (setup)      : Atil = basis_rom PT_U^-1 for all six reductors in ONE block-diagonal GEMM, once per model,
+//                  so that sum_q theta_q A_q == sum_k f_k Atil_k and no theta solve is left per step  (:491-492)
+//   dgemm (K)    : [K | M] = F^T Atil -- sum_q theta_q A_q^r for 5 operators, K = bdf M + dt(...)
 //                  accumulated in one pass; M is emitted at the k-boundary (hook)   (:445, rom.py:906)
 //   dgemm (f)    : reduced forcing  dt * basis_rhs theta_rhs
 //   k_lu_solve   : b = M w + f, dense LU with partial pivoting in shared memory, u = K^-1 b  (rom.py:492)
@@ -713,15 +714,17 @@ struct Carver {
 };
 
 struct SweepBuffers {
-    double *basis_cat, *basis_rhs, *Ccat, *Invcat, *Tpad;
+    double *basis_cat, *basis_rhs, *basis_til, *rhs_til, *Ccat, *Invcat, *Tpad;
     int2* kt_ranges;
-    double *Phi, *Ustar, *Wv, *Un, *Unm1, *TU, *F, *Theta, *Kmat, *Mmat, *From;
+    double *Phi, *Ustar, *Wv, *Un, *Unm1, *TU, *F, *Kmat, *Mmat, *From;
 };
 
 size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
     const size_t Bcp = pl.Bcpad;
     b.basis_cat = c.take<double>((size_t)pl.Qmat * pl.ldk);
     b.basis_rhs = c.take<double>((size_t)pl.mpad[kRhs] * pl.Npad);
+    b.basis_til = c.take<double>((size_t)pl.Qmat * pl.ldk);
+    b.rhs_til = c.take<double>((size_t)pl.mpad[kRhs] * pl.Npad);
     b.Ccat = c.take<double>((size_t)pl.Qall * RT_NF);
     b.Invcat = c.take<double>((size_t)pl.Qall * pl.Qall);
     b.Tpad = c.take<double>((size_t)pl.mpad[kTril] * pl.Npad);
@@ -734,7 +737,6 @@ size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
     b.Unm1 = c.take<double>(Bcp * pl.Npad);
     b.TU = c.take<double>((size_t)pl.mpad[kTril] * Bcp);
     b.F = c.take<double>((size_t)pl.Qall * Bcp);
-    b.Theta = c.take<double>((size_t)pl.Qall * Bcp);
     b.Kmat = c.take<double>(Bcp * pl.ldk);
     b.Mmat = c.take<double>(Bcp * pl.ldk);
     b.From = c.take<double>(Bcp * pl.Npad);
@@ -877,6 +879,25 @@ int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_ev
         RT_CUDA(h, cudaMemcpyAsync(b.kt_ranges, host_ranges, tiles * sizeof(int2), cudaMemcpyHostToDevice, st));
         RT_CUDA(h, cudaStreamSynchronize(st));  // host_ranges is on the stack
     }
+    // ---- fold the interpolation solves into the bases, once per model:
+    //   sum_q theta_q A_q with theta = PT_U^-1 f   ==   sum_k f_k Atil_k,   Atil_k = sum_q (PT_U^-1)[q][k] A_q
+    // so a time step goes from the sampled entries straight to the assembly GEMM (no per-step theta GEMM).
+    if (pl.Qmat > 0) {
+        dg::Operand oa{b.Invcat, pl.Qmat, pl.Qmat, 1, pl.Qall}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
+        dg::Params p = dg::default_params();
+        p.C = b.basis_til; p.ldc_m = pl.ldk; p.ldc_n = 1;
+        p.kt_ranges = b.kt_ranges;
+        int rc2 = dg::launch(h, oa, ob, p, st);
+        if (rc2) return rc2;
+    }
+    if (pl.m[kRhs] > 0) {
+        const double* inv_rhs = b.Invcat + (size_t)pl.qoff[kRhs] * pl.Qall + pl.qoff[kRhs];
+        dg::Operand oa{inv_rhs, pl.mpad[kRhs], pl.mpad[kRhs], 1, pl.Qall}, ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
+        dg::Params p = dg::default_params();
+        p.C = b.rhs_til; p.ldc_m = pl.Npad; p.ldc_n = 1;
+        int rc2 = dg::launch(h, oa, ob, p, st);
+        if (rc2) return rc2;
+    }
     return RT_OK;
 }
 
@@ -917,17 +938,9 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
         k_entries<<<egrid, 256, 0, st>>>(pl, b.Ccat, b.Phi, cx.has_T ? b.TU : nullptr, dt, b.F);
         RT_LAUNCH_CHECK(h);
     }
-    {   ProfScope ps(prof, pa, 3, st);  // theta = PT_U^-1 f, all reductors, block-diagonal
-        dg::Operand oa{b.Invcat, pl.Qall, pl.Qall, pl.Qall, 1}, ob{b.F, pl.Bc, pl.Qall, 1, pl.Bcpad};
-        dg::Params p = dg::default_params();
-        p.C = b.Theta; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
-        p.kt_ranges = b.kt_ranges;
-        rc = dg::launch(h, oa, ob, p, st);
-        if (rc) return rc;
-    }
     if (pl.Qmat > 0) {
         ProfScope ps(prof, pa, 4, st);  // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
-        dg::Operand oa{b.Theta, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_cat, pl.N2, pl.Qmat, 1, pl.ldk};
+        dg::Operand oa{b.F, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_til, pl.N2, pl.Qmat, 1, pl.ldk};
         dg::Params p = dg::default_params();
         p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
         p.C2 = b.Mmat; p.hook_kt = pl.mpad[0] / 16; p.hook_scale = bdfc;
@@ -948,8 +961,8 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     }
     if (pl.m[kRhs] > 0) {
         ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
-        dg::Operand oa{b.Theta + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
-        dg::Operand ob{b.basis_rhs, pl.N, pl.mpad[kRhs], 1, pl.Npad};
+        dg::Operand oa{b.F + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
+        dg::Operand ob{b.rhs_til, pl.N, pl.mpad[kRhs], 1, pl.Npad};
         dg::Params p = dg::default_params();
         p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
         rc = dg::launch(h, oa, ob, p, st);
