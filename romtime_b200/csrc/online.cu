@@ -11,7 +11,8 @@
 //   dgemm (K)    : [K | M] = F^T Atil -- sum_q theta_q A_q^r for 5 operators, K = bdf M + dt(...)
 //                  accumulated in one pass; M is emitted at the k-boundary (hook)   (:445, rom.py:906)
 //   dgemm (f)    : reduced forcing  dt * basis_rhs theta_rhs
-//   k_lu_solve   : b = M w + f, dense LU with partial pivoting in shared memory, u = K^-1 b  (rom.py:492)
+//   solve        : b = M w + f, u = K^-1 b with partial pivoting (rom.py:492): k_gj_smem (blocked Gauss-Jordan on DMMA
+//                  tiles, 32 < N <= 64), k_lu_shift (register LU, N <= 32), k_lu_solve (shared-memory LU, N > 64)
 // All GEMMs run on the TMA + DMMA core (dgemm_tma.cuh).  No collective: parameters are independent.
 #include <utility>
 #include <vector>
@@ -317,14 +318,7 @@ __global__ void __launch_bounds__(kLuThreads) k_lu_solve(SweepPlan pl, const dou
     }
 }
 
-// ------------------------------------------------------------------ register-resident LU (N <= 64)
-// The shared-memory LU above is bound by shared-memory bandwidth (3 accesses per FMA).  Here every
-// thread keeps ONE ROW of [K | b] in registers (NP + 1 doubles, NP = 32 or 64 = threads per CTA; rows
-// and columns beyond N are identity padding).  Per elimination step: warp-shuffle arg-max of the
-// pivot column among unpivoted rows (implicit partial pivoting, first maximum like dgetrf), the
-// winning thread of each warp publishes its row in shared memory, ONE barrier, every unpivoted row
-// updates itself with broadcast (conflict-free) reads.  U rows are then written in pivot order and
-// warp 0 back-substitutes.
+// ------------------------------------------------------------------ staging helper of the register-resident LU
 // coalesced staging of an N x N row-major matrix into padded shared memory: warp w takes rows w, w+NW, ...;
 // 16 rows (32 loads per lane) are issued before the first store so that one round trip covers them
 template <int NW, int LD>
@@ -353,150 +347,8 @@ __device__ __forceinline__ void stage_matrix(double* __restrict__ stage, const d
     }
 }
 
-// one elimination step with compile-time k (keeps the row in registers: every index is static)
-template <int NP, int K>
-__device__ __forceinline__ void lu_step(double (&r)[NP + 1], bool& done, bool& sing, int& order, double* piv,
-                                        unsigned long long (*cand)[NP / 32], int t, int lane, int warp) {
-    constexpr int NW = NP / 32;
-    constexpr int PV = NP + 2;
-    // arg-max key: |r_k| with the 7 low mantissa bits replaced by (candidate flag, 63 - t): the largest
-    // magnitude wins, the lowest row index on (near-)ties; two redux.sync instead of a shuffle tree
-    const unsigned long long key =
-        done ? 0ull : ((unsigned long long)__double_as_longlong(fabs(r[K])) & ~127ull) | 64ull | (unsigned long long)(63 - t);
-    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
-    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
-    constexpr int par = K & 1;
-    double* mine = piv + (par * NW + warp) * PV;
-    if (lo == ml && hi == mh && !done) {
-        // warp winner publishes its row [K..NP] plus the reciprocal pivot in slot NP+1 (16-byte stores)
-        const double rinv = 1.0 / r[K];
-#pragma unroll
-        for (int j2 = (K & ~1); j2 < NP; j2 += 2) *reinterpret_cast<double2*>(mine + j2) = make_double2(r[j2], r[j2 + 1]);
-        *reinterpret_cast<double2*>(mine + NP) = make_double2(r[NP], rinv);
-    }
-    if (lane == 0) cand[par][warp] = ((unsigned long long)mh << 32) | ml;
-    __syncthreads();
-    int ww = 0;
-    unsigned long long gk = cand[par][0];
-#pragma unroll
-    for (int w = 1; w < NW; ++w)
-        if (cand[par][w] > gk) { gk = cand[par][w]; ww = w; }
-    const int gt = 63 - (int)(gk & 63ull);
-    const double* pr = piv + (par * NW + ww) * PV;
-    if (t == gt) {
-        done = true;
-        order = K;
-        if (r[K] == 0.0) sing = true;
-    } else if (!done) {
-        const double2 tail = *reinterpret_cast<const double2*>(pr + NP);
-        const double l = r[K] * tail.y;
-        if ((K & 1) == 0) r[K + 1] = fma(-l, pr[K + 1], r[K + 1]);
-#pragma unroll
-        for (int j2 = ((K + 2) & ~1); j2 < NP; j2 += 2) {
-            const double2 q = *reinterpret_cast<const double2*>(pr + j2);
-            r[j2] = fma(-l, q.x, r[j2]);
-            r[j2 + 1] = fma(-l, q.y, r[j2 + 1]);
-        }
-        r[NP] = fma(-l, tail.x, r[NP]);
-    }
-}
-template <int NP, int... Ks>
-__device__ __forceinline__ void lu_steps(double (&r)[NP + 1], bool& done, bool& sing, int& order, double* piv,
-                                         unsigned long long (*cand)[NP / 32], int t, int lane, int warp,
-                                         std::integer_sequence<int, Ks...>) {
-    (lu_step<NP, Ks>(r, done, sing, order, piv, cand, t, lane, warp), ...);
-}
-
-template <int NP>
-__global__ void __launch_bounds__(NP, (NP == 64 ? 6 : 8)) k_lu_reg(SweepPlan pl, const double* __restrict__ Kmat,
-                                                                 const double* __restrict__ Mmat,
-                                                                 const double* __restrict__ From, const double* __restrict__ Wv,
-                                                                 LuExtras ex, double* __restrict__ Un, double* __restrict__ Unm1,
-                                                                 double* __restrict__ uN_out, int64_t out_stride_p,
-                                                                 int64_t out_off, int* __restrict__ info, int step) {
-    constexpr int LD = NP + 1;
-    constexpr int NW = NP / 32;
-    constexpr int PV = NP + 2;
-    extern __shared__ __align__(16) double sm[];
-    double* piv = sm;                        // 2 * NW * PV   (16-byte aligned rows)
-    double* wv = piv + 2 * NW * PV;          // NP
-    double* rdiag = wv + NP;                 // NP
-    double* stage = rdiag + NP;              // NP * LD
-    __shared__ unsigned long long cand[2][NW];
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int N = pl.N;
-    const int64_t p = blockIdx.x;
-    const double* Kp = Kmat + p * pl.ldk;
-    const double* Mp = Mmat + p * pl.ldk;
-
-    stage_matrix<NW, LD>(stage, Mp, ex.Madd ? ex.Madd + p * N * N : nullptr, N, warp, lane);
-    wv[t] = t < N ? Wv[p * pl.Npad + t] : 0.0;
-    __syncthreads();
-    double bt = 0.0;
-    if (t < N) {
-        double b0 = 0.0, b1 = 0.0;
-        int j = 0;
-        for (; j + 1 < N; j += 2) { b0 = fma(stage[t * LD + j], wv[j], b0); b1 = fma(stage[t * LD + j + 1], wv[j + 1], b1); }
-        if (j < N) b0 = fma(stage[t * LD + j], wv[j], b0);
-        bt = (b0 + b1) + From[p * pl.Npad + t];
-        if (ex.fadd) bt += ex.fadd[p * N + t];
-    }
-    __syncthreads();
-    stage_matrix<NW, LD>(stage, Kp, ex.Kadd ? ex.Kadd + p * N * N : nullptr, N, warp, lane);
-    __syncthreads();
-    double r[NP + 1];
-#pragma unroll
-    for (int j = 0; j < NP; ++j) r[j] = (t < N && j < N) ? stage[t * LD + j] : (j == t ? 1.0 : 0.0);
-    r[NP] = bt;
-    __syncthreads();
-
-    bool done = false, sing = false;
-    int order = 0;
-    lu_steps<NP>(r, done, sing, order, piv, cand, t, lane, warp, std::make_integer_sequence<int, NP>{});
-    // U rows (and the transformed right-hand side) in pivot order
-#pragma unroll
-    for (int j = 0; j <= NP; ++j)
-        if (j >= order) stage[order * LD + j] = r[j];
-#pragma unroll
-    for (int j = 0; j < NP; ++j)
-        if (j == order) rdiag[order] = 1.0 / r[j];
-    __syncthreads();
-    if (warp == 0) {
-        double xv[NW];
-#pragma unroll
-        for (int q = 0; q < NW; ++q) xv[q] = stage[(q * 32 + lane) * LD + NP];
-#pragma unroll
-        for (int kr = NW - 1; kr >= 0; --kr) {
-#pragma unroll 4
-            for (int kl = 31; kl >= 0; --kl) {
-                const int k = kr * 32 + kl;
-                const double xk = __shfl_sync(0xffffffffu, xv[kr], kl) * rdiag[k];
-                if (lane == kl) xv[kr] = xk;
-#pragma unroll
-                for (int er = 0; er <= kr; ++er) {
-                    const int e = er * 32 + lane;
-                    if (e < k) xv[er] = fma(-stage[e * LD + k], xk, xv[er]);
-                }
-            }
-        }
-#pragma unroll
-        for (int q = 0; q < NW; ++q) {
-            const int e = q * 32 + lane;
-            if (e < N) {
-                const int64_t s = p * pl.ldu + e;
-                Unm1[s] = Un[s];
-                Un[s] = xv[q];
-                if (uN_out) uN_out[p * out_stride_p + out_off + e] = xv[q];
-            }
-        }
-    }
-    if (sing) atomicCAS(&info[p], 0, step + 1);
-}
-
-
-// ------------------------------------------------------------------ register-resident LU, shifting rows (N <= 64)
-// Same data layout as k_lu_reg (thread t keeps row t of [K | b] in registers) with a RUNTIME loop over the
+// ------------------------------------------------------------------ register-resident LU, shifting rows (used for N <= 32)
+// Thread t keeps row t of [K | b] in registers (rows / columns beyond N are identity padding); RUNTIME loop over the
 // elimination steps: after step k every row is shifted left by one while it is updated
 // (r[j-1] = r[j] - l * u[j]), so the pivot column is always r[0] and every register index stays static.  The
 // loop body is ~100 instructions instead of 13,000 unrolled ones (no instruction-cache misses), and per step
@@ -626,9 +478,257 @@ __global__ void __launch_bounds__(NP, (NP == 64 ? 5 : 8)) k_lu_shift(SweepPlan p
     if (sing) atomicCAS(&info[p], 0, step + 1);
 }
 
+__device__ __forceinline__ void dmma884(double2& c, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c.x), "+d"(c.y)
+                 : "d"(a), "d"(b));
+}
+
+// element pair (i, j), (i, j + 1) of the identity-padded N x N row-major matrix A (+ optional dense term)
+__device__ __forceinline__ double2 gj_load2(const double* __restrict__ A, const double* __restrict__ add, int N, bool vec,
+                                            int i, int j) {
+    double2 v;
+    if (vec && i < N && j < N) {
+        v = __ldg(reinterpret_cast<const double2*>(A + i * N + j));
+    } else {
+        v.x = (i < N && j < N) ? __ldg(A + i * N + j) : (i == j ? 1.0 : 0.0);
+        v.y = (i < N && j + 1 < N) ? __ldg(A + i * N + j + 1) : (i == j + 1 ? 1.0 : 0.0);
+    }
+    if (add) {
+        if (i < N && j < N) v.x += __ldg(add + i * N + j);
+        if (i < N && j + 1 < N) v.y += __ldg(add + i * N + j + 1);
+    }
+    return v;
+}
+
+// ------------------------------------------------------------------ blocked Gauss-Jordan on DMMA tiles (32 < N <= 64)
+// u = K^-1 b by Gauss-Jordan elimination with implicit partial pivoting, in 16 panels of 4 columns:
+//   panel:    4 pivot steps on the 64 x 4 panel held in registers (lane l: rows l and l + 32).  Arg-max over the
+//             rows that were not pivots yet (one redux.sync on a 32-bit key), the pivot record travels by shuffle,
+//             the pivot column is eliminated in EVERY other row.  The 4 steps compose to
+//                 X <- X - W Xraw[pivot rows]
+//             with a 64 x 4 matrix W accumulated next to the panel (3 DFMA per row and step).
+//   trailing: every live 8 x 8 tile gets ONE mma.sync.m8n8k4.f64:  C -= W_tile (8 x 4) * Xraw[pivot rows] (4 x 8).
+// After 16 panels the matrix is a row-permuted diagonal: x_k = rhs[piv_k] / pivot_k -- no triangular solves, no
+// stored factors.  The right-hand side b = M w + f rides along as a vector.
+// The padded 64 x 64 matrix lives in shared memory as 8 x 8 tiles in DMMA accumulator order (tile (rt, ct) =
+// 32 lanes x double2: one conflict-free LDS.128 / STS.128 per tile), so a CTA needs 80 registers per thread and
+// six parameters are resident per SM.  Four warps per parameter:
+//   warp 0 (panel warp): applies the pending update W_p to the tile column that holds panel p + 1, then factors
+//           panel p + 1 (no block barrier inside a panel) and updates the right-hand side;
+//   warps 1-3: apply W_p to the other live tile columns (look-ahead: this overlaps the next panel).
+// One block barrier per panel.  The raw pivot rows (B operand) and -W (A operand) are read straight from shared
+// memory; a tile column is always updated by ONE warp, which loads its B fragment before storing any tile.
+struct GjsShared {
+    double2 tiles[64 * 32];  // tile (rt, ct) at (rt * 8 + ct) * 32, lane-major
+    double pw[2][64 * 4];    // -W of panel p (parity p & 1), A-fragment order (row * 4 + k)
+    double rhs[64];
+    int gr[2][4];            // pivot rows of panel p (parity p & 1)
+};
+
+struct GjsPanelState {
+    bool done0, done1, sing;
+    double rd0, rd1;  // lane l: reciprocal pivots of columns l and l + 32
+    int pv0, pv1;     //         and their pivot rows
+};
+
+template <int J>
+__device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4], GjsPanelState& ps,
+                                         int (&gr)[4], int col, int lane) {
+    const double ri0 = 1.0 / a0[J], ri1 = 1.0 / a1[J];  // both candidates: off the arg-max chain
+    // key: high word of |a_J|, 7 low bits = (candidate flag, 63 - row): the pivot is within 2^-13 of the column maximum
+    const unsigned k0 = ps.done0 ? 0u : (((unsigned)__double2hiint(a0[J]) & 0x7fffff80u) | 64u | (unsigned)(63 - lane));
+    const unsigned k1 = ps.done1 ? 0u : (((unsigned)__double2hiint(a1[J]) & 0x7fffff80u) | 64u | (unsigned)(31 - lane));
+    const bool sel = k1 > k0;
+    double rec[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) rec[j] = j < J ? (sel ? w1[j] : w0[j]) : (j == J ? (sel ? ri1 : ri0) : (sel ? a1[j] : a0[j]));
+    const unsigned mx = __reduce_max_sync(0xffffffffu, sel ? k1 : k0);
+    const int g = 63 - (int)(mx & 63u);
+    const int src = g & 31;
+    double r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) r[j] = __shfl_sync(0xffffffffu, rec[j], src);
+    gr[J] = g;
+    const bool me0 = g == lane, me1 = g == lane + 32;
+    if ((me0 && a0[J] == 0.0) || (me1 && a1[J] == 0.0)) ps.sing = true;
+    const double l0 = me0 ? 0.0 : a0[J] * r[J];
+    const double l1 = me1 ? 0.0 : a1[J] * r[J];
+#pragma unroll
+    for (int j = J + 1; j < 4; ++j) { a0[j] = fma(-l0, r[j], a0[j]); a1[j] = fma(-l1, r[j], a1[j]); }
+#pragma unroll
+    for (int j = 0; j < J; ++j) { w0[j] = fma(-l0, r[j], w0[j]); w1[j] = fma(-l1, r[j], w1[j]); }
+    w0[J] = l0;
+    w1[J] = l1;
+    ps.done0 |= me0;
+    ps.done1 |= me1;
+    if (lane == (col & 31)) {
+        if (col < 32) { ps.rd0 = r[J]; ps.pv0 = g; }
+        else { ps.rd1 = r[J]; ps.pv1 = g; }
+    }
+}
+
+// warp 0: factor panel pn (columns 4 pn .. 4 pn + 3); publishes -W and the pivot rows under parity pn & 1
+__device__ __forceinline__ void gjs_factor(GjsShared& sh, GjsPanelState& ps, int pn, int lane) {
+    const int ct = pn >> 1, h = pn & 1, par = pn & 1;
+    double a0[4], a1[4], w0[4] = {0.0, 0.0, 0.0, 0.0}, w1[4] = {0.0, 0.0, 0.0, 0.0};
+    {
+        const int b0 = ((lane >> 3) * 8 + ct) * 32 + (lane & 7) * 4 + 2 * h;
+        const int b1 = b0 + 4 * 8 * 32;  // row + 32: four row tiles further
+        const double2 x0 = sh.tiles[b0], x1 = sh.tiles[b0 + 1], y0 = sh.tiles[b1], y1 = sh.tiles[b1 + 1];
+        a0[0] = x0.x; a0[1] = x0.y; a0[2] = x1.x; a0[3] = x1.y;
+        a1[0] = y0.x; a1[1] = y0.y; a1[2] = y1.x; a1[3] = y1.y;
+    }
+    int gr[4];
+    gjs_step<0>(a0, a1, w0, w1, ps, gr, 4 * pn + 0, lane);
+    gjs_step<1>(a0, a1, w0, w1, ps, gr, 4 * pn + 1, lane);
+    gjs_step<2>(a0, a1, w0, w1, ps, gr, 4 * pn + 2, lane);
+    gjs_step<3>(a0, a1, w0, w1, ps, gr, 4 * pn + 3, lane);
+    double2* pw2 = reinterpret_cast<double2*>(sh.pw[par]);
+    pw2[2 * lane] = make_double2(-w0[0], -w0[1]);
+    pw2[2 * lane + 1] = make_double2(-w0[2], -w0[3]);
+    pw2[2 * (lane + 32)] = make_double2(-w1[0], -w1[1]);
+    pw2[2 * (lane + 32) + 1] = make_double2(-w1[2], -w1[3]);
+    if (lane < 4) sh.gr[par][lane] = lane == 0 ? gr[0] : (lane == 1 ? gr[1] : (lane == 2 ? gr[2] : gr[3]));
+    // right-hand side: rhs <- rhs - W rhs_raw[pivot rows]
+    double s0 = sh.rhs[lane], s1 = sh.rhs[lane + 32];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const double rp = sh.rhs[gr[k]]; s0 = fma(-w0[k], rp, s0); s1 = fma(-w1[k], rp, s1); }
+    __syncwarp();
+    sh.rhs[lane] = s0;
+    sh.rhs[lane + 32] = s1;
+}
+
+// one warp: tile column ct <- tile column ct - W_p * Xraw[pivot rows of panel p]
+__device__ __forceinline__ void gjs_update_col(GjsShared& sh, const double (&af)[8], int ct, int par, bool own_half, int lane) {
+    const int g8 = lane >> 2, q = lane & 3;
+    const int r = sh.gr[par][q];
+    const double* tl = reinterpret_cast<const double*>(sh.tiles);
+    double bf = tl[((r >> 3) * 8 + ct) * 64 + ((r & 7) * 4 + (g8 >> 1)) * 2 + (g8 & 1)];
+    if (own_half && g8 < 4) bf = 0.0;  // the panel's own columns are finished
+    double2 c[8];
+#pragma unroll
+    for (int rt = 0; rt < 8; ++rt) c[rt] = sh.tiles[(rt * 8 + ct) * 32 + lane];
+#pragma unroll
+    for (int rt = 0; rt < 8; ++rt) dmma884(c[rt], af[rt], bf);
+#pragma unroll
+    for (int rt = 0; rt < 8; ++rt) sh.tiles[(rt * 8 + ct) * 32 + lane] = c[rt];
+}
+
+__global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* __restrict__ Kmat, const double* __restrict__ Mmat,
+                                                    const double* __restrict__ From, const double* __restrict__ Wv, LuExtras ex,
+                                                    double* __restrict__ Un, double* __restrict__ Unm1,
+                                                    double* __restrict__ uN_out, int64_t out_stride_p, int64_t out_off,
+                                                    int* __restrict__ info, int step) {
+    __shared__ __align__(16) GjsShared sh;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int g8 = lane >> 2, q = lane & 3;
+    const int N = pl.N;
+    const bool vec = (N & 1) == 0;
+    const int64_t p = blockIdx.x;
+    const double* Kp = Kmat + p * pl.ldk;
+    const double* Mp = Mmat + p * pl.ldk;
+    const double* Ka = ex.Kadd ? ex.Kadd + p * N * N : nullptr;
+    const double* Ma = ex.Madd ? ex.Madd + p * N * N : nullptr;
+
+    // ---- b = M w + f (thread t: row t / 2, every other column pair, partner summed by shuffle) and K into the tiles
+    if (t < 64) sh.pw[0][t] = t < N ? __ldg(Wv + p * pl.Npad + t) : 0.0;  // w staged in the (still unused) W buffer
+    const int row = t >> 1, hp = t & 1;
+    double s0 = 0.0, s1 = 0.0;
+    if (N == 64 && !Ma && !Ka) {
+        // fast path: four batches of eight 16-byte loads, two batches in flight
+        const double2* mrow = reinterpret_cast<const double2*>(Mp + row * 64) + hp;
+        const double2* ktile = reinterpret_cast<const double2*>(Kp + g8 * 64 + 2 * q);  // + (8 rt) * 64 + 8 ct doubles
+        double2 b0[8], b1[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) b0[i] = __ldg(mrow + 2 * i);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) b1[i] = __ldg(mrow + 2 * (i + 8));
+        __syncthreads();  // w visible
+        const double2* w2 = reinterpret_cast<const double2*>(sh.pw[0]) + hp;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const double2 wv = w2[2 * i]; s0 = fma(b0[i].x, wv.x, s0); s1 = fma(b0[i].y, wv.y, s1); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const int idx = w * 16 + i; b0[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const double2 wv = w2[2 * (i + 8)]; s0 = fma(b1[i].x, wv.x, s0); s1 = fma(b1[i].y, wv.y, s1); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const int idx = w * 16 + 8 + i; b1[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + lane] = b0[i];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lane] = b1[i];
+    } else {
+        __syncthreads();
+        if (row < N) {
+            for (int j = 2 * hp; j < N; j += 4) {
+                const double2 m = gj_load2(Mp, Ma, N, vec, row, j);
+                s0 = fma(m.x, sh.pw[0][j], s0);
+                if (j + 1 < N) s1 = fma(m.y, sh.pw[0][j + 1], s1);
+            }
+        }
+#pragma unroll 4
+        for (int i = 0; i < 16; ++i) {
+            const int idx = w * 16 + i, rt = idx >> 3, ct = idx & 7;
+            sh.tiles[idx * 32 + lane] = gj_load2(Kp, Ka, N, vec, 8 * rt + g8, 8 * ct + 2 * q);
+        }
+    }
+    {
+        double s = s0 + s1;
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        if (hp == 0) {
+            if (row < N) {
+                s += From[p * pl.Npad + row];
+                if (ex.fadd) s += ex.fadd[p * N + row];
+            }
+            sh.rhs[row] = s;
+        }
+    }
+    __syncthreads();
+
+    GjsPanelState ps;
+    ps.done0 = ps.done1 = ps.sing = false;
+    ps.rd0 = ps.rd1 = 0.0;
+    ps.pv0 = ps.pv1 = 0;
+    if (w == 0) gjs_factor(sh, ps, 0, lane);
+    __syncthreads();
+#pragma unroll 1
+    for (int pn = 0; pn < 15; ++pn) {
+        const int T = pn >> 1, h = pn & 1, par = pn & 1;
+        const int first = h == 0 ? T : T + 1;  // first live tile column = the one that holds panel pn + 1
+        double af[8];
+#pragma unroll
+        for (int rt = 0; rt < 8; ++rt) af[rt] = sh.pw[par][32 * rt + lane];
+        if (w == 0) {
+            gjs_update_col(sh, af, first, par, h == 0, lane);
+            __syncwarp();
+            gjs_factor(sh, ps, pn + 1, lane);
+        } else {
+            for (int ct = first + w; ct < 8; ct += 3) gjs_update_col(sh, af, ct, par, false, lane);
+        }
+        __syncthreads();
+    }
+    // ---- x_k = rhs[piv_k] / pivot_k, history shuffle, output
+    if (w == 0) {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int e = lane + 32 * hh;
+            if (e < N) {
+                const double x = hh ? sh.rhs[ps.pv1] * ps.rd1 : sh.rhs[ps.pv0] * ps.rd0;
+                const int64_t s = p * pl.ldu + e;
+                Unm1[s] = Un[s];
+                Un[s] = x;
+                if (uN_out) uN_out[p * out_stride_p + out_off + e] = x;
+            }
+        }
+        if (ps.sing) atomicCAS(&info[p], 0, step + 1);
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------ stand-alone entry points
+
 extern "C" int rt_invert_f64(rt_handle* h, const double* A, int64_t m, double* Ainv, int* info, void* stream) {
     if (!h) return RT_EINVAL;
     RT_REQUIRE(h, A && Ainv && info && m >= 1 && m <= 160);
@@ -777,6 +877,12 @@ int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, cons
     }
     k_lu_shift<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
                                             o.info, o.step);
+    RT_LAUNCH_CHECK(h);
+    return RT_OK;
+}
+
+int launch_gj(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o, cudaStream_t st) {
+    k_gj_smem<<<pl.Bc, 128, 0, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off, o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
@@ -973,7 +1079,7 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     ProfScope ps_lu(prof, pa, 6, st);
     const int R = (pl.N + 31) / 32;
     if (pl.N <= 32) rc = launch_lu_reg<32>(h, pl, b, ex, o, st);
-    else if (pl.N <= 64) rc = launch_lu_reg<64>(h, pl, b, ex, o, st);
+    else if (pl.N <= 64) rc = launch_gj(h, pl, b, ex, o, st);
     else switch (R) {
         case 1: rc = launch_lu<1>(h, pl, b, ex, o, st); break;
         case 2: rc = launch_lu<2>(h, pl, b, ex, o, st); break;

@@ -98,7 +98,8 @@ def test_golden_sweep(golden, bdf):
         assert np.array_equal(last.cpu().numpy(), u[:, :, -1])
 
 
-@pytest.mark.parametrize("N,m,m_rhs,B,nt", [(64, 16, 16, 200, 12), (64, 128, 128, 140, 6), (33, 20, 9, 7, 10)])
+@pytest.mark.parametrize("N,m,m_rhs,B,nt", [(64, 16, 16, 200, 12), (64, 128, 128, 140, 6), (33, 20, 9, 7, 10), (50, 12, 12, 9, 8),
+                                               (63, 10, 10, 5, 6)])
 def test_sweep_vs_oracle(N, m, m_rhs, B, nt):
     from romtime_b200 import kernels
 
@@ -125,3 +126,33 @@ def test_sweep_multi_chunk_consistency():
     for b in (0, 4735, 4736, 4999):
         ref = orc.rom_sweep(model, mus[b], 5, 1e-3, bdf2=True)
         assert relerr(last[b], ref[:, -1]) < 1e-10
+
+
+@pytest.mark.parametrize("N", [5, 32, 33, 40, 63, 64, 100])
+def test_dense_solve_needs_pivoting(N):
+    """The per-parameter solver (LU for N <= 32 and N > 64, blocked Gauss-Jordan on DMMA tiles in between) must
+    pivot: a row-permuted diagonally dominant matrix has zeros (or tiny entries) on its diagonal."""
+    from romtime_b200.rom.rom import _dense_solve
+
+    rng = np.random.default_rng(N)
+    A = rng.standard_normal((N, N)) + N * np.eye(N)
+    perm = rng.permutation(N)
+    K = A[perm]  # K[i] = A[perm[i]]: the large entries sit at (i, perm[i])
+    b = rng.standard_normal(N)
+    x = _dense_solve(K, b)
+    assert relerr(x, np.linalg.solve(K, b)) < 1e-10
+    # wide dynamic range inside every column: the pivot must be the large entry, not the first one
+    K2 = K * np.logspace(-6, 6, N)[rng.permutation(N)][:, None]
+    x2 = _dense_solve(K2, b)
+    assert relerr(x2, np.linalg.solve(K2, b)) < 1e-10
+
+
+@pytest.mark.parametrize("N", [20, 48, 64, 90])
+def test_dense_solve_singular_raises(N):
+    from romtime_b200.rom.rom import _dense_solve
+
+    rng = np.random.default_rng(N + 1)
+    K = rng.standard_normal((N, N))
+    K[:, N // 2] = 0.0  # exactly singular: a zero pivot column whatever the row order
+    with pytest.raises(np.linalg.LinAlgError):
+        _dense_solve(K, rng.standard_normal(N))

@@ -1,0 +1,32 @@
+// Dependent-issue latencies on B200 of the instructions on the pivot chain: DFMA, DMUL, MUFU.RCP64H, DMMA, SHFL, redux.
+#include <cstdio>
+#include <cuda_runtime.h>
+template <int OP>
+__global__ void k(double* out, long long* cyc, int iters, double a, double b) {
+    double x = threadIdx.x * 1e-3 + 1.0, y = 2.0;
+    unsigned u = threadIdx.x;
+    long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+        if (OP == 0) { x = fma(x, a, b); }
+        if (OP == 1) { x = x * a; }
+        if (OP == 2) { x = 1.0 / x; }
+        if (OP == 3) { asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(x), "+d"(y) : "d"(a), "d"(b)); }
+        if (OP == 4) { x = __shfl_sync(0xffffffffu, x, (threadIdx.x + 1) & 31); }
+        if (OP == 5) { u = __reduce_max_sync(0xffffffffu, u) + threadIdx.x; }
+        if (OP == 6) { x = fma(x, a, b); u = (u * 3u) ^ (unsigned)i; }
+    }
+    long long t1 = clock64();
+    if (threadIdx.x == 0) cyc[OP] = t1 - t0;
+    if (x + y + u == 123.456) out[0] = x;
+}
+int main() {
+    double* out; long long* cyc; cudaMalloc(&out, 8); cudaMallocManaged(&cyc, 64);
+    const int it = 4096;
+    k<0><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<1><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
+    k<2><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<3><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
+    k<4><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<5><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
+    cudaDeviceSynchronize();
+    const char* nm[] = {"dfma", "dmul", "rcp(1/x)", "dmma884", "shfl64", "redux_max+add"};
+    for (int i = 0; i < 6; ++i) printf("%s: %.1f cycles per dependent op\n", nm[i], (double)cyc[i] / it);
+    return 0;
+}
