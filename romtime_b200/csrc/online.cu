@@ -186,24 +186,125 @@ __global__ void __launch_bounds__(256) k_entries_ext(SweepPlan pl, const double*
 }
 
 // F[q][p] = scale_op * ( sum_f Ccat[q][f] Phi[f][p] + [trilinear] b0_p * TU[q - qoff][p] )
-__global__ void __launch_bounds__(256) k_entries(SweepPlan pl, const double* __restrict__ Ccat, const double* __restrict__ Phi,
+// blockIdx.y = a group of 16 rows q (operator blocks start at multiples of 16, so a group has ONE operator);
+// the group's 16 x RT_NF coefficients are staged in shared memory, one thread per parameter.
+__global__ void __launch_bounds__(128) k_entries(SweepPlan pl, const double* __restrict__ Ccat, const double* __restrict__ Phi,
                                                  const double* __restrict__ TU, double dt, double* __restrict__ F) {
-    const int p = blockIdx.x * 256 + threadIdx.x;
+    __shared__ double cs[16 * RT_NF];
+    const int q0 = blockIdx.y * 16;
+    for (int e = threadIdx.x; e < 16 * RT_NF; e += 128) cs[e] = Ccat[(int64_t)q0 * RT_NF + e];
+    __syncthreads();
+    const int p = blockIdx.x * 128 + threadIdx.x;
     if (p >= pl.Bc) return;
+    int op = 0;
+    while (q0 >= pl.qoff[op + 1]) ++op;
+    const int k0 = q0 - pl.qoff[op];
+    const int nvalid = pl.m[op] - k0 < 16 ? pl.m[op] - k0 : 16;  // rows beyond m[op] are zero padding
     double phi[RT_NF];
 #pragma unroll
     for (int f = 0; f < RT_NF; ++f) phi[f] = Phi[(int64_t)f * pl.Bcpad + p];
-    const int q0 = blockIdx.y * 32;
-    for (int q = q0; q < q0 + 32 && q < pl.Qall; ++q) {
-        int op = 0;
-        while (q >= pl.qoff[op + 1]) ++op;
-        if (q - pl.qoff[op] >= pl.m[op]) { F[(int64_t)q * pl.Bcpad + p] = 0.0; continue; }  // zero padding row
-        const double* c = Ccat + (int64_t)q * RT_NF;
+    const bool tril = op == kTril && TU != nullptr;
+    const double scale = op == 0 ? 1.0 : dt;
+#pragma unroll 4
+    for (int r = 0; r < 16; ++r) {
         double v = 0.0;
+        if (r < nvalid) {
 #pragma unroll
-        for (int f = 0; f < RT_NF; ++f) v = fma(c[f], phi[f], v);
-        if (op == kTril && TU) v = fma(phi[11], TU[(int64_t)(q - pl.qoff[kTril]) * pl.Bcpad + p], v);
-        F[(int64_t)q * pl.Bcpad + p] = (op == 0) ? v : dt * v;
+            for (int f = 0; f < RT_NF; ++f) v = fma(cs[r * RT_NF + f], phi[f], v);
+            if (tril) v = fma(phi[11], TU[(int64_t)(k0 + r) * pl.Bcpad + p], v);
+            v *= scale;
+        }
+        F[(int64_t)(q0 + r) * pl.Bcpad + p] = v;
+    }
+}
+
+// Skinny products of the step (N <= 64, m <= 128): 32 parameters per CTA on the FP64 FMA pipe.  On the 128 x 128
+// tiles of the GEMM core they fill 37 of 148 SMs and pay a pipeline fill each; here every SM takes 32 parameters.
+//   TU[q][p] = sum_j T[q][j] u*[p][j]        (trilinear sampled entries, deim/nonlinear.py:247-283)
+// thread (pp = t % 32, qg = t / 32): 16 rows q for one parameter; T and the 32 u* rows are staged in shared memory
+__global__ void __launch_bounds__(256) k_tu(SweepPlan pl, const double* __restrict__ Tpad, const double* __restrict__ Ustar,
+                                            int mT, double* __restrict__ TU) {
+    extern __shared__ __align__(16) double sm_tu[];
+    const int Np = pl.Npad, ldu = Np + 2;
+    double* Ts = sm_tu;            // 128 x Np (rows >= mT zero)
+    double* us = Ts + 128 * Np;    // 32 x ldu
+    const int t = threadIdx.x, pp = t & 31, qg = t >> 5;
+    const int64_t p0 = (int64_t)blockIdx.x * 32;
+#pragma unroll 8
+    for (int e = t; e < 128 * Np; e += 256) Ts[e] = e < mT * Np ? Tpad[e] : 0.0;
+#pragma unroll 8
+    for (int e = t; e < 32 * Np; e += 256) {
+        const int r = e / Np, j = e - r * Np;
+        us[r * ldu + j] = p0 + r < pl.Bc ? Ustar[(p0 + r) * Np + j] : 0.0;
+    }
+    __syncthreads();
+    double acc[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) acc[r] = 0.0;
+    const double* trow = Ts + qg * 16 * Np;
+    for (int j = 0; j < Np; j += 2) {
+        const double2 u = *reinterpret_cast<const double2*>(us + pp * ldu + j);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const double2 tv = *reinterpret_cast<const double2*>(trow + r * Np + j);
+            acc[r] = fma(tv.x, u.x, acc[r]);
+            acc[r] = fma(tv.y, u.y, acc[r]);
+        }
+    }
+    if (p0 + pp < pl.Bc) {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const int q = qg * 16 + r;
+            if (q < mT) TU[(int64_t)q * pl.Bcpad + p0 + pp] = acc[r];
+        }
+    }
+}
+
+//   From[p][i] = sum_k F_rhs[k][p] rhs_til[k][i]     (reduced forcing, rom.py:911-929)
+// thread (pp = t % 32, ig = t / 32): 8 components i for one parameter
+__global__ void __launch_bounds__(256) k_forcing(SweepPlan pl, const double* __restrict__ Frhs, const double* __restrict__ rhs_til,
+                                                 int mp, double* __restrict__ From) {
+    // both operands are staged with every load of the CTA in flight at once (an L2 round trip per k otherwise)
+    extern __shared__ __align__(16) double sm_f[];
+    double* fs = sm_f;             // F_rhs[k][32 parameters of this CTA]
+    double* rs = sm_f + 128 * 32;  // rhs_til (mp x Npad)
+    const int t = threadIdx.x, pp = t & 31, i0 = (t >> 5) * 8;
+    const int Np = pl.Npad;
+    const int64_t p0 = (int64_t)blockIdx.x * 32;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        const int k = (t >> 5) + 8 * e;
+        fs[k * 32 + pp] = (k < mp && p0 + pp < pl.Bc) ? Frhs[(int64_t)k * pl.Bcpad + p0 + pp] : 0.0;
+    }
+    {
+        const double2* src = reinterpret_cast<const double2*>(rhs_til);
+        double2* dst = reinterpret_cast<double2*>(rs);
+        const int n2 = mp * Np / 2;
+#pragma unroll 16
+        for (int e = t; e < n2; e += 256) dst[e] = __ldg(src + e);
+    }
+    __syncthreads();
+    if (i0 >= Np) return;
+    double acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < mp; ++k) {
+        const double f = fs[k * 32 + pp];
+        const double* r = rs + k * Np + i0;
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) {
+            if (i0 + e < Np) {  // Npad is even: the pair is inside the row
+                const double2 rv = *reinterpret_cast<const double2*>(r + e);
+                acc[e] = fma(f, rv.x, acc[e]);
+                acc[e + 1] = fma(f, rv.y, acc[e + 1]);
+            }
+        }
+    }
+    if (p0 + pp < pl.Bc) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+            if (i0 + e < Np) From[(p0 + pp) * Np + i0 + e] = acc[e];
     }
 }
 
@@ -1034,14 +1135,26 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     } else {
         if (cx.has_T) {
             ProfScope ps(prof, pa, 1, st);
-            dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
-            dg::Params p = dg::default_params();
-            p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
-            rc = dg::launch(h, oa, ob, p, st);
-            if (rc) return rc;
+            if (pl.N <= 64 && pl.m[kTril] <= 128) {
+                const size_t smem = ((size_t)128 * pl.Npad + 32 * (pl.Npad + 2)) * sizeof(double);
+                static bool attr_set = false;
+                if (!attr_set) {
+                    RT_CUDA(h, cudaFuncSetAttribute(k_tu, cudaFuncAttributeMaxDynamicSharedMemorySize, (128 * 64 + 32 * 66) * 8));
+                    attr_set = true;
+                }
+                k_tu<<<(unsigned)ceil_div64(pl.Bc, 32), 256, smem, st>>>(pl, b.Tpad, b.Ustar, pl.m[kTril], b.TU);
+                RT_LAUNCH_CHECK(h);
+            } else {
+                dg::Operand oa{b.Tpad, pl.m[kTril], pl.Npad, pl.Npad, 1}, ob{b.Ustar, pl.Bc, pl.Npad, pl.Npad, 1};
+                dg::Params p = dg::default_params();
+                p.C = b.TU; p.ldc_m = pl.Bcpad; p.ldc_n = 1;
+                rc = dg::launch(h, oa, ob, p, st);
+                if (rc) return rc;
+            }
         }
         ProfScope ps(prof, pa, 2, st);
-        k_entries<<<egrid, 256, 0, st>>>(pl, b.Ccat, b.Phi, cx.has_T ? b.TU : nullptr, dt, b.F);
+        const dim3 egrid2((unsigned)ceil_div64(pl.Bc, 128), (unsigned)(pl.Qall / 16));
+        k_entries<<<egrid2, 128, 0, st>>>(pl, b.Ccat, b.Phi, cx.has_T ? b.TU : nullptr, dt, b.F);
         RT_LAUNCH_CHECK(h);
     }
     if (pl.Qmat > 0) {
@@ -1067,12 +1180,24 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     }
     if (pl.m[kRhs] > 0) {
         ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
-        dg::Operand oa{b.F + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
-        dg::Operand ob{b.rhs_til, pl.N, pl.mpad[kRhs], 1, pl.Npad};
-        dg::Params p = dg::default_params();
-        p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
-        rc = dg::launch(h, oa, ob, p, st);
-        if (rc) return rc;
+        if (pl.N <= 64 && pl.mpad[kRhs] <= 128) {
+            static bool attr_set = false;
+            if (!attr_set) {
+                RT_CUDA(h, cudaFuncSetAttribute(k_forcing, cudaFuncAttributeMaxDynamicSharedMemorySize, (128 * 32 + 128 * 64) * 8));
+                attr_set = true;
+            }
+            const size_t smem = ((size_t)128 * 32 + (size_t)pl.mpad[kRhs] * pl.Npad) * sizeof(double);
+            k_forcing<<<(unsigned)ceil_div64(pl.Bc, 32), 256, smem, st>>>(pl, b.F + (size_t)pl.qoff[kRhs] * pl.Bcpad, b.rhs_til,
+                                                                      pl.mpad[kRhs], b.From);
+            RT_LAUNCH_CHECK(h);
+        } else {
+            dg::Operand oa{b.F + (size_t)pl.qoff[kRhs] * pl.Bcpad, pl.Bc, pl.mpad[kRhs], 1, pl.Bcpad};
+            dg::Operand ob{b.rhs_til, pl.N, pl.mpad[kRhs], 1, pl.Npad};
+            dg::Params p = dg::default_params();
+            p.C = b.From; p.ldc_m = pl.Npad; p.ldc_n = 1;
+            rc = dg::launch(h, oa, ob, p, st);
+            if (rc) return rc;
+        }
     } else {
         RT_CUDA(h, cudaMemsetAsync(b.From, 0, (size_t)pl.Bc * pl.Npad * sizeof(double), st));
     }
