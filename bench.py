@@ -63,7 +63,7 @@ def reference_arm(a, out_fd):
     import cpu_bench
 
     cores = os.cpu_count() or 1
-    nt = 20
+    nt = 300  # bounded sample per bench step: a few seconds on every core
     for _ in range(max(a.warmup, 0) and 1):
         cpu_bench.online_sweep_rate(cores, 64, a.m, 2)
     t0 = time.perf_counter()
@@ -210,7 +210,7 @@ def main():
         import cpu_bench
 
         cores = os.cpu_count() or 1
-        nt_cpu = 40
+        nt_cpu = 1000  # one full C5 trajectory per core: 10-20 s of CPU work
         rate, wall, _ = cpu_bench.online_sweep_rate(cores, 64, a.m, nt_cpu)
         cpu_baseline = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"oracle rom_sweep (NumPy port of rom/rom.py:430-555): {cores} parameters x {nt_cpu} "
@@ -304,8 +304,8 @@ def main():
                 "unit": "TFLOP/s", "frac": ach / peak,
                 "peak_source": "FP64 DMMA peak measured in this run (rt_fp64_peak_tflops; MEASURED_PEAKS.json has no fp64 entry)",
                 "avg_launch_ms": g_ms / g_n, "launches_timed": g_n, "share_of_step": g_ms / total_prof,
-                "traffic": 335.4e6,
-                "traffic_source": "dram bytes read+write per launch, ncu --set full, profiles/r1_sweep_ncu.md",
+                "traffic": 318.7e6,
+                "traffic_source": "dram bytes read+write per launch, ncu --set full, profiles/r1b_sweep_ncu.md",
                 "kernel_shares": {k: v[0] / total_prof for k, v in prof.items()}}
 
     pod = None

@@ -633,6 +633,9 @@ struct GjsPanelState {
     int pv0, pv1;     //         and their pivot rows
 };
 
+#ifndef GJS_REDUX_BROADCAST
+#define GJS_REDUX_BROADCAST 1
+#endif
 template <int J>
 __device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4], GjsPanelState& ps,
                                          int (&gr)[4], int col, int lane) {
@@ -648,8 +651,22 @@ __device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], doubl
     const int g = 63 - (int)(mx & 63u);
     const int src = g & 31;
     double r[4];
+#if GJS_REDUX_BROADCAST
+    // broadcast by or-reduction: redux.sync does not queue behind the tile traffic of the trailing warps in the
+    // shared-memory pipe the way shuffles do
+    {
+        const bool is_src = lane == src;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const unsigned lo = __reduce_or_sync(0xffffffffu, is_src ? (unsigned)__double2loint(rec[j]) : 0u);
+            const unsigned hi = __reduce_or_sync(0xffffffffu, is_src ? (unsigned)__double2hiint(rec[j]) : 0u);
+            r[j] = __hiloint2double((int)hi, (int)lo);
+        }
+    }
+#else
 #pragma unroll
     for (int j = 0; j < 4; ++j) r[j] = __shfl_sync(0xffffffffu, rec[j], src);
+#endif
     gr[J] = g;
     const bool me0 = g == lane, me1 = g == lane + 32;
     if ((me0 && a0[J] == 0.0) || (me1 && a1[J] == 0.0)) ps.sing = true;

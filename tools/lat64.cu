@@ -13,7 +13,19 @@ __global__ void k(double* out, long long* cyc, int iters, double a, double b) {
         if (OP == 3) { asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(x), "+d"(y) : "d"(a), "d"(b)); }
         if (OP == 4) { x = __shfl_sync(0xffffffffu, x, (threadIdx.x + 1) & 31); }
         if (OP == 5) { u = __reduce_max_sync(0xffffffffu, u) + threadIdx.x; }
-        if (OP == 6) { x = fma(x, a, b); u = (u * 3u) ^ (unsigned)i; }
+        if (OP == 6) {  // 8 independent or-reductions (broadcast of 4 doubles without the MIO pipe)
+            unsigned r0 = __reduce_or_sync(0xffffffffu, u), r1 = __reduce_or_sync(0xffffffffu, u + 1), r2 = __reduce_or_sync(0xffffffffu, u + 2),
+                     r3 = __reduce_or_sync(0xffffffffu, u + 3), r4 = __reduce_or_sync(0xffffffffu, u + 4), r5 = __reduce_or_sync(0xffffffffu, u + 5),
+                     r6 = __reduce_or_sync(0xffffffffu, u + 6), r7 = __reduce_or_sync(0xffffffffu, u + 7);
+            u = (r0 ^ r1 ^ r2 ^ r3 ^ r4 ^ r5 ^ r6 ^ r7) + threadIdx.x;
+        }
+        if (OP == 7) {  // 8 independent 32-bit shuffles (= 4 doubles)
+            const int src = (u + i) & 31;
+            unsigned r0 = __shfl_sync(0xffffffffu, u, src), r1 = __shfl_sync(0xffffffffu, u + 1, src), r2 = __shfl_sync(0xffffffffu, u + 2, src),
+                     r3 = __shfl_sync(0xffffffffu, u + 3, src), r4 = __shfl_sync(0xffffffffu, u + 4, src), r5 = __shfl_sync(0xffffffffu, u + 5, src),
+                     r6 = __shfl_sync(0xffffffffu, u + 6, src), r7 = __shfl_sync(0xffffffffu, u + 7, src);
+            u = (r0 ^ r1 ^ r2 ^ r3 ^ r4 ^ r5 ^ r6 ^ r7) + threadIdx.x;
+        }
     }
     long long t1 = clock64();
     if (threadIdx.x == 0) cyc[OP] = t1 - t0;
@@ -25,8 +37,9 @@ int main() {
     k<0><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<1><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     k<2><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<3><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     k<4><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<5><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
+    k<6><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<7><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     cudaDeviceSynchronize();
-    const char* nm[] = {"dfma", "dmul", "rcp(1/x)", "dmma884", "shfl64", "redux_max+add"};
-    for (int i = 0; i < 6; ++i) printf("%s: %.1f cycles per dependent op\n", nm[i], (double)cyc[i] / it);
+    const char* nm[] = {"dfma", "dmul", "rcp(1/x)", "dmma884", "shfl64", "redux_max+add", "8x redux_or group", "8x shfl32 group"};
+    for (int i = 0; i < 8; ++i) printf("%s: %.1f cycles per dependent op\n", nm[i], (double)cyc[i] / it);
     return 0;
 }
