@@ -905,15 +905,23 @@ inline int64_t pad16(int64_t x) { return (x + 15) & ~int64_t(15); }
 // the chunk (a multiple of 128, at most 40*128 so that the K/M buffers stay ~330 MB) is chosen to
 // minimise the total number of tile waves over the whole batch, i.e. the wave-quantisation loss of the
 // dominant kernel: 37*128 parameters x 32 tiles = 8 full waves of 148 for N = 64 on a B200.
-int64_t plan_chunk(int64_t B, int tiles_n, int sms) {
+int64_t plan_chunk(int64_t B, int N, int sms) {
+    const int tiles_n = (int)ceil_div64((int64_t)N * N, dg::BN);
     const int64_t rows_total = ceil_div64(B, 128);
+    // the solve kernel has its own quantisation: k_gj_smem keeps 6 parameters per SM resident (one "solve wave" =
+    // 6 * sms parameters, 0.4 of a GEMM tile wave at N = 64); 4736 parameters are 5.33 such waves, 14208 exactly 16
+    const bool gj = N > 32 && N <= 64;
+    const int64_t solve_wave = 6 * (int64_t)sms;
+    const double solve_weight = gj ? 0.4 : 0.0;
     int64_t best_k = 1;
     double best_cost = 1e300;
-    for (int64_t k = 1; k <= 40; ++k) {
+    for (int64_t k = 1; k <= 120; ++k) {
         const int64_t nfull = rows_total / k, rem = rows_total - nfull * k;
+        const int64_t rem_params = B - nfull * k * 128 > 0 ? B - nfull * k * 128 : 0;
         const double waves = (double)nfull * (double)ceil_div64(k * tiles_n, sms) + (double)ceil_div64(rem * tiles_n, sms);
+        const double swaves = (double)nfull * (double)ceil_div64(k * 128, solve_wave) + (double)ceil_div64(rem_params, solve_wave);
         const double chunks = (double)(nfull + (rem ? 1 : 0));
-        const double cost = waves + 0.25 * chunks;  // per-chunk-step fixed cost of the small kernels, in waves
+        const double cost = waves + solve_weight * swaves + 0.25 * chunks;  // + per-chunk-step cost of the small kernels
         if (cost < best_cost - 1e-9) { best_cost = cost; best_k = k; }
     }
     return best_k * 128;
@@ -1050,7 +1058,7 @@ int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_ev
     pl.Qall = off;
     pl.Qmat = pl.qoff[kRhs];
     RT_REQUIRE(h, pl.Qall >= 1);
-    cx.chunk = plan_chunk(B, (pl.N2 + dg::BN - 1) / dg::BN, h->sm_count);
+    cx.chunk = plan_chunk(B, pl.N, h->sm_count);
     const int64_t Bc_max = B < cx.chunk ? B : cx.chunk;
     pl.Bcpad = (int)(ceil_div64(Bc_max, 128) * 128);
     pl.Bc = (int)Bc_max;
@@ -1307,7 +1315,7 @@ extern "C" int rt_online_step_f64(rt_handle* h, const rt_rom_model* model, const
 
 extern "C" int64_t rt_sweep_chunk(int64_t B, int N, int sm_count) {
     if (B < 1 || N < 1 || sm_count < 1) return 0;
-    return plan_chunk(B, (int)ceil_div64((int64_t)N * N, dg::BN), sm_count);
+    return plan_chunk(B, N, sm_count);
 }
 
 extern "C" int rt_profile_enable(rt_handle* h, int on) {

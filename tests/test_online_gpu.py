@@ -115,15 +115,23 @@ def test_sweep_vs_oracle(N, m, m_rhs, B, nt):
 
 
 def test_sweep_multi_chunk_consistency():
-    """More parameters than one chunk (4736): every chunk must reproduce the single-parameter run."""
+    """More parameters than one chunk: every chunk (and both sides of the chunk boundary) must reproduce the
+    single-parameter run."""
+    import torch
+
     from romtime_b200 import kernels
 
-    model = synthetic.make_piston_model(N=16, m=16, seed=3)
-    mus = synthetic.sample_mus(5000, seed=11)
+    N, B = 64, 18000
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    chunk = int(kernels.load_library().rt_sweep_chunk(B, N, sms))
+    assert 0 < chunk < B, chunk
+    model = synthetic.make_piston_model(N=N, m=16, seed=3)
+    mus = synthetic.sample_mus(B, seed=11)
     dm = kernels.DeviceRomModel(model)
     last, info = kernels.online_sweep(dm, mus, 5, 1e-3, bdf=2, history=False)
     last = last.cpu().numpy()
-    for b in (0, 4735, 4736, 4999):
+    assert not info.cpu().numpy().any()
+    for b in (0, chunk - 1, chunk, B - 1):
         ref = orc.rom_sweep(model, mus[b], 5, 1e-3, bdf2=True)
         assert relerr(last[b], ref[:, -1]) < 1e-10
 
