@@ -274,9 +274,9 @@ def main():
     hist_host = torch.empty((Bl, nt, N), dtype=torch.float64).pin_memory()
 
     def step_e2e():
-        md = mus_host.to(dev, non_blocking=True)
-        o, i = kernels.online_sweep(dm, md, nt, dt, bdf=2, history=True)
-        hist_host.copy_(o, non_blocking=True)
+        # public host-to-host call: mus from pinned host memory, the history lands in pinned host memory (the
+        # device-to-host copy of a chunk overlaps the next chunk's sweep)
+        kernels.online_sweep_to_host(dm, mus_host, nt, dt, bdf=2, out_host=hist_host)
         torch.cuda.synchronize()
 
     step_e2e()

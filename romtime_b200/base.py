@@ -41,7 +41,7 @@ class RomSolutionsStorage(SolutionsStorage):
 
 class RomBatchSolutions:
     """Result of a batched sweep: ``rom_device`` is a CUDA tensor (B, nt, N) -- [b, n, :] the reduced
-    solution of parameter b after step n; ``info`` (B,) int32, 0 = ok, n+1 = zero pivot at step n."""
+    solution of parameter b after step n (a pinned host tensor after ``solve_batch(..., to_host=True)``); ``info`` (B,) int32, 0 = ok, n+1 = zero pivot at step n."""
 
     def __init__(self, ts, mus, rom_device, info, basis=None):
         self.ts = np.asarray(ts, dtype=float)
@@ -64,7 +64,7 @@ class RomBatchSolutions:
 
         if self._basis is None:
             raise ValueError("no reduced basis attached to this batch")
-        return kernels.pod_lift(self._basis, self.rom_device[b].t().contiguous(), order="C").cpu().numpy()
+        return kernels.pod_lift(self._basis, kernels.to_device(self.rom_device[b]).t().contiguous(), order="C").cpu().numpy()
 
     def storage(self, b, domain=None, lifting=None):
         """A reference-style RomSolutionsStorage for parameter b."""

@@ -336,6 +336,50 @@ def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
     return out, info
 
 
+def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=None):
+    """The sweep with the history delivered in (pinned) HOST memory: parameters are processed in the chunks the
+    library plans (rt_sweep_chunk); the device-to-host copy of chunk c runs on a side stream while chunk c + 1 is
+    computed, through two device staging buffers.  ``mus``: (B, 3) host array / tensor (pinned for an asynchronous
+    upload).  Returns (uN host tensor (B, nt, N), info int32 cuda tensor (B,))."""
+    if not dev_model.has_evaluator:
+        raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
+    mh = mus if isinstance(mus, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(mus, dtype=np.float64))
+    mh = mh.reshape(-1, 3)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    B, N = mh.shape[0], dev_model.N
+    if out_host is None:
+        out_host = torch.empty((B, nt, N), dtype=F64).pin_memory()
+    lib = load_library()
+    h = handle(dev.index)
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    chunk = max(1, min(B, int(lib.rt_sweep_chunk(B, N, sms))))
+    info = torch.empty(B, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        main = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        bufs = [torch.empty((chunk, nt, N), dtype=F64, device=dev) for _ in range(2 if B > chunk else 1)]
+        copied = [None, None]
+        for c, p0 in enumerate(range(0, B, chunk)):
+            n = min(chunk, B - p0)
+            buf = bufs[c % len(bufs)]
+            if copied[c % 2] is not None:
+                main.wait_event(copied[c % 2])  # the staging buffer is free again
+            md = mh[p0:p0 + n].to(dev, non_blocking=True).contiguous()
+            rc = lib.rt_online_sweep_f64(h, ctypes.byref(dev_model.struct), _ptr(md), n, nt, float(dt), int(bdf), _ptr(buf),
+                                         _ptr(info[p0:p0 + n]), stream_ptr())
+            check(rc, h, "rt_online_sweep_f64")
+            done = torch.cuda.Event()
+            done.record(main)
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                out_host[p0:p0 + n].copy_(buf[:n], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            copied[c % 2] = ev
+        main.wait_stream(side)
+    return out_host, info
+
+
 PROFILE_CLASSES = ("state", "gemm_Tu", "entries", "gemm_theta", "gemm_assembly", "gemm_forcing", "lu_solve", "unused")
 
 

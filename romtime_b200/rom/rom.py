@@ -419,11 +419,12 @@ class RomConstructor(Reductor):
         return idx_mu
 
     # ------------------------------------------------------------------ online: a batch of parameters
-    def solve_batch(self, mus, evaluator, nt=None, dt=None, bdf=None, history=True, step=Stage.ONLINE):
+    def solve_batch(self, mus, evaluator, nt=None, dt=None, bdf=None, history=True, step=Stage.ONLINE, to_host=False):
         """Sweep B parameters at once on the device.  ``mus``: (B, 3) array [a0, omega, delta] or a list
         of mu dictionaries; ``evaluator``: a ``PistonEvaluator`` with the closed-form sampled-entry tables.
         Under ``torch.distributed`` every rank passes ITS shard of ``mus`` (see distributed.shard_range);
-        there is no collective.  Returns a ``RomBatchSolutions``."""
+        there is no collective.  ``to_host=True`` delivers the history in pinned host memory, the copy of one chunk of
+        parameters overlapping the sweep of the next (kernels.online_sweep_to_host).  Returns a ``RomBatchSolutions``."""
         from .. import kernels
 
         fom = self.fom
@@ -441,7 +442,10 @@ class RomConstructor(Reductor):
         for m in mu_list:
             self.add_mu(mu=m, step=step)
         dm = self._device_model(evaluator)
-        out, info = kernels.online_sweep(dm, arr, nt, dt, bdf=bdf, history=history)
+        if to_host and history:
+            out, info = kernels.online_sweep_to_host(dm, arr, nt, dt, bdf=bdf)
+        else:
+            out, info = kernels.online_sweep(dm, arr, nt, dt, bdf=bdf, history=history)
         ts = dt * np.arange(1, nt + 1)
         if not history:
             out = out.unsqueeze(1)

@@ -134,6 +134,11 @@ def test_sweep_multi_chunk_consistency():
     for b in (0, chunk - 1, chunk, B - 1):
         ref = orc.rom_sweep(model, mus[b], 5, 1e-3, bdf2=True)
         assert relerr(last[b], ref[:, -1]) < 1e-10
+    # host-delivered history: chunked sweep with the device-to-host copy of a chunk overlapping the next chunk
+    hist, info_h = kernels.online_sweep_to_host(dm, mus, 5, 1e-3, bdf=2)
+    assert hist.shape == (B, 5, N) and not hist.is_cuda
+    assert not info_h.cpu().numpy().any()
+    assert np.array_equal(hist[:, -1, :].numpy(), last)
 
 
 @pytest.mark.parametrize("N", [5, 32, 33, 40, 63, 64, 100])
