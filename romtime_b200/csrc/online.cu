@@ -639,15 +639,17 @@ struct GjsPanelState {
 template <int J>
 __device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4], GjsPanelState& ps,
                                          int (&gr)[4], int col, int lane) {
-    const double ri0 = 1.0 / a0[J], ri1 = 1.0 / a1[J];  // both candidates: off the arg-max chain
     // key: high word of |a_J|, 7 low bits = (candidate flag, 63 - row): the pivot is within 2^-13 of the column maximum
     const unsigned k0 = ps.done0 ? 0u : (((unsigned)__double2hiint(a0[J]) & 0x7fffff80u) | 64u | (unsigned)(63 - lane));
     const unsigned k1 = ps.done1 ? 0u : (((unsigned)__double2hiint(a1[J]) & 0x7fffff80u) | 64u | (unsigned)(31 - lane));
     const bool sel = k1 > k0;
+    const unsigned mx = __reduce_max_sync(0xffffffffu, sel ? k1 : k0);
+    // reciprocal of the lane's own candidate, issued AFTER the reduction so that its dependent chain runs beside it
+    double rinv_loc;
+    asm volatile("rcp.rn.f64 %0, %1;" : "=d"(rinv_loc) : "d"(sel ? a1[J] : a0[J]));
     double rec[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) rec[j] = j < J ? (sel ? w1[j] : w0[j]) : (j == J ? (sel ? ri1 : ri0) : (sel ? a1[j] : a0[j]));
-    const unsigned mx = __reduce_max_sync(0xffffffffu, sel ? k1 : k0);
+    for (int j = 0; j < 4; ++j) rec[j] = j < J ? (sel ? w1[j] : w0[j]) : (j == J ? rinv_loc : (sel ? a1[j] : a0[j]));
     const int g = 63 - (int)(mx & 63u);
     const int src = g & 31;
     double r[4];
