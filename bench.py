@@ -308,6 +308,46 @@ def main():
                 "traffic_source": "dram bytes read+write per launch, ncu --set full, profiles/r1b_sweep_ncu.md",
                 "kernel_shares": {k: v[0] / total_prof for k, v in prof.items()}}
 
+    # ---- certification leg: S-ROM estimator over every (parameter, step) of the last sweep
+    cert = None
+    try:
+        g = torch.Generator(device=dev).manual_seed(1006)
+        Vs = torch.linalg.qr(torch.randn((20000, N), dtype=torch.float64, device=dev, generator=g))[0]
+        srom = out + 1e-3 * torch.randn(out.shape, dtype=torch.float64, device=dev, generator=g)
+        G, _ = kernels.pod_gram(Vs, normalize=False)
+        kernels.rom_difference(out, srom, Vs)
+        torch.cuda.synchronize()
+        c0, c1, c2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        c0.record()
+        err = kernels.rom_difference(out, srom, Vs)
+        c1.record()
+        summ = kernels.errors_summary(err)
+        c2.record()
+        torch.cuda.synchronize()
+        t_est, t_sum = c0.elapsed_time(c1), c1.elapsed_time(c2)
+        rows = float(Bl) * nt
+        cert = {"rows": int(rows), "estimator_ms": t_est, "summary_ms": t_sum,
+                "estimator_GBps": 8.0 * rows * (2 * N + 1) / t_est * 1e-6, "estimator_tflops": 2.0 * rows * N * N / t_est * 1e-9,
+                "estimator_frac_of_fp64_peak": 2.0 * rows * N * N / t_est * 1e-9 / peak,
+                "bound": "fp64 pipe (2 Nhat^2 flop vs 8 (N + Nhat) bytes per row: 8 flop/B, ridge 5.7)",
+                "max_err": float(err.max().item())}
+        if rank == 0 and world == 1 and not a.skip_cpu:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import romtime_oracle as orc_mod
+
+            nb = 64
+            hu, hs, hv = out[:nb].cpu().numpy(), srom[:nb].cpu().numpy(), Vs.cpu().numpy()
+            t0 = time.perf_counter()
+            ref = orc_mod.rom_difference_batch(hu, hs, hv)
+            wall = time.perf_counter() - t0
+            cert["cpu_rows_per_s"] = nb * nt / wall
+            cert["cpu_sample"] = f"oracle rom_difference_batch (utils.py:173-212 per row), {nb} parameters x {nt} steps, 1 core, {wall:.1f} s"
+            cert["gpu_rows_per_s"] = rows / (t_est * 1e-3)
+            cert["parity_max_rel"] = float(abs(err[:nb].cpu().numpy() - ref).max() / abs(ref).max())
+        del srom, err, summ, Vs
+    except Exception as exc:  # report, never hide
+        cert = {"error": repr(exc)}
+
     pod = None
     if not a.skip_pod:
         try:
@@ -323,7 +363,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Bl * 3 * 8) * world,
                     "d2h_bytes_per_step": int(Bl * nt * N * 8) * world},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_baseline,
-            "pod": pod, "singular_solves": bad,
+            "pod": pod, "certification": cert, "singular_solves": bad,
         }
         emit(line, out_fd)
     if world > 1:

@@ -206,6 +206,19 @@ int rt_profile_read(rt_handle* h, double* ms, int64_t* launches);
 /* number of kernels launched by this handle since creation (bench.py "gpu_launches") */
 int64_t rt_launch_count(const rt_handle* h);
 
+/* ---------------------------------------------- certification (rom/hrom.py:504-626) -------- */
+/* S-ROM error estimator of utils.compute_rom_difference (utils.py:173-212) for every (parameter, step) of a pair
+ * of sweeps:  err[b*nt + n] = || V_srom (uN_srom[b, n, :] - pad(uN[b, n, :])) ||_2 / sqrt(Nh).
+ * uN (B x nt x N) and uN_srom (B x nt x Nhat, N <= Nhat <= 128) are the device histories of rt_online_sweep_f64;
+ * G (Nhat x Nhat row-major) = V_srom^T V_srom, e.g. from rt_pod_gram_f64 with normalize = 0; Nh = rows of V_srom. */
+int rt_rom_difference_f64(rt_handle* h, const double* uN, int64_t B, int64_t nt, int64_t N,
+                          const double* uN_srom, int64_t Nhat, const double* G, int64_t Nh, double* err,
+                          void* stream);
+
+/* Reductor.create_errors_summary (rom/base.py:154-163) on the device: err (B x nt) ->
+ * summary (B x 4 row-major) = {mean, median, max, min} over the nt steps of every parameter; nt <= 16384. */
+int rt_errors_summary_f64(rt_handle* h, const double* err, int64_t B, int64_t nt, double* summary, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -374,6 +374,39 @@ def gen_treewalk():
     print("treewalk:", {k: v.shape for k, v in out.items() if k.endswith("basis_fom") or k.endswith("basis")})
 
 
+def gen_certification():
+    """S-ROM estimator and error summaries: the reference's own compute_rom_difference
+    (utils.py:173-212), Reductor._compute_error (rom/base.py:52-73) and create_errors_summary (:154-163)."""
+    ref = ref_harness.load_reference()
+    from romtime.rom.base import Reductor
+    from romtime.utils import compute_rom_difference
+
+    rng = np.random.default_rng(1006)
+    out = {}
+    cases = [("ortho", 300, 10, 14, 6, 20), ("general", 257, 33, 40, 5, 17), ("equal", 128, 64, 64, 4, 9),
+             ("wide", 500, 20, 96, 3, 12)]
+    out["names"] = np.array([c[0] for c in cases])
+    for name, Nh, N, Nhat, B, nt in cases:
+        V = rng.standard_normal((Nh, Nhat))
+        if name == "ortho":
+            V, _ = np.linalg.qr(V)
+        uN = rng.standard_normal((B, nt, N))
+        uS = rng.standard_normal((B, nt, Nhat))
+        uS[:, :, :N] += uN  # S-ROM = ROM + a correction, as in the certification loop
+        err = np.array([[compute_rom_difference(uN[b, n], uS[b, n], V) for n in range(nt)] for b in range(B)])
+        red = Reductor(grid=None)
+        for b in range(B):
+            red.errors_rom[b] = list(err[b])
+        red.create_errors_summary()
+        summ = red.summary_errors[["mean", "median", "max", "min"]].to_numpy(dtype=float)
+        rms = np.array([Reductor._compute_error(uS[b, n], np.append(uN[b, n], (Nhat - N) * [0.0])) for b in range(B)
+                        for n in range(nt)]).reshape(B, nt)
+        for k, v in (("V", V), ("uN", uN), ("uS", uS), ("err", err), ("summary", summ), ("rms", rms)):
+            out[f"{name}/{k}"] = v
+    np.savez_compressed(os.path.join(GOLD, "certification.npz"), **out)
+    print("certification:", {k: v.shape for k, v in out.items() if k.endswith("err")})
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     ref_harness.load_reference()
@@ -382,5 +415,6 @@ if __name__ == "__main__":
     gen_project_interp()
     gen_solve()
     gen_treewalk()
+    gen_certification()
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))

@@ -138,6 +138,17 @@ def compute_rom_difference(uN, uN_srom, V_srom):
     return np.linalg.norm(lincomb, ord=2) / np.sqrt(len(lincomb))
 
 
+def rom_difference_batch(uN, uN_srom, V_srom):
+    """compute_rom_difference for every (parameter, step): uN (B, nt, N), uN_srom (B, nt, Nhat) -> (B, nt)."""
+    B, nt, _ = uN_srom.shape
+    return np.array([[compute_rom_difference(uN[b, n], uN_srom[b, n], V_srom) for n in range(nt)] for b in range(B)])
+
+
+def errors_summary(err):
+    """create_errors_summary per parameter: columns mean, median, max, min.  rom/base.py:154-163."""
+    return np.array([[np.mean(e), np.median(e), np.max(e), np.min(e)] for e in err])
+
+
 def rms_error(u, ue):
     """Reductor._compute_error.  rom/base.py:52-73."""
     return np.linalg.norm(u - ue, ord=2) / np.sqrt(len(u))

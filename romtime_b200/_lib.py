@@ -66,6 +66,8 @@ SIGNATURES = {
     "rt_online_sweep_last_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_i64, c_dbl, c_int, c_vp, c_vp, c_vp]),
     "rt_online_step_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_dbl, c_int, c_i64, c_vp, c_vp, c_vp, c_vp,
                                    c_vp, c_vp, c_vp]),
+    "rt_rom_difference_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp]),
+    "rt_errors_summary_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp]),
     "rt_sweep_chunk": (c_i64, [c_i64, c_int, c_int]),
     "rt_profile_enable": (c_int, [c_vp, c_int]),
     "rt_profile_read": (c_int, [c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(c_i64)]),

@@ -380,6 +380,41 @@ def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=No
     return out_host, info
 
 
+def rom_difference(uN, uN_srom, V_srom):
+    """rt_rom_difference_f64: the S-ROM estimator of utils.compute_rom_difference for every (parameter, step).
+    uN (B, nt, N), uN_srom (B, nt, Nhat) device (or host) histories, V_srom (Nh, Nhat).  Returns err (B, nt) cuda."""
+    a, b = to_device(uN).contiguous(), to_device(uN_srom).contiguous()
+    if a.dim() != 3 or b.dim() != 3 or a.shape[:2] != b.shape[:2]:
+        raise ValueError("uN and uN_srom must be (B, nt, N) and (B, nt, Nhat) histories of the same sweep")
+    V = to_device(V_srom)
+    Nh, Nhat = V.shape
+    if b.shape[2] != Nhat or a.shape[2] > Nhat:
+        raise ValueError("V_srom must have one column per S-ROM coefficient and the S-ROM must contain the ROM")
+    G, _ = pod_gram(V, normalize=False)
+    G = G.contiguous()
+    B, nt, N = a.shape
+    err = torch.empty((B, nt), dtype=F64, device=a.device)
+    h = handle(a.device.index)
+    with torch.cuda.device(a.device):
+        rc = load_library().rt_rom_difference_f64(h, _ptr(a), B, nt, N, _ptr(b), Nhat, _ptr(G), Nh, _ptr(err), stream_ptr())
+    check(rc, h, "rt_rom_difference_f64")
+    return err
+
+
+def errors_summary(err):
+    """rt_errors_summary_f64: err (B, nt) -> (B, 4) cuda tensor {mean, median, max, min} per parameter."""
+    e = to_device(err).contiguous()
+    if e.dim() != 2:
+        raise ValueError("err must be (B, nt)")
+    B, nt = e.shape
+    out = torch.empty((B, 4), dtype=F64, device=e.device)
+    h = handle(e.device.index)
+    with torch.cuda.device(e.device):
+        rc = load_library().rt_errors_summary_f64(h, _ptr(e), B, nt, _ptr(out), stream_ptr())
+    check(rc, h, "rt_errors_summary_f64")
+    return out
+
+
 PROFILE_CLASSES = ("state", "gemm_Tu", "entries", "gemm_theta", "gemm_assembly", "gemm_forcing", "lu_solve", "unused")
 
 

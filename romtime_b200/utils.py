@@ -76,6 +76,27 @@ def compute_rom_difference(uN, uN_srom, V_srom):
     return np.linalg.norm(lincomb, ord=2) / np.sqrt(len(lincomb))
 
 
+def compute_rom_difference_batch(uN, uN_srom, V_srom):
+    """compute_rom_difference for every (parameter, step) of two batched sweeps, on the device
+    (rt_rom_difference_f64): uN (B, nt, N) and uN_srom (B, nt, Nhat) as ``RomBatchSolutions.rom_device`` holds them,
+    V_srom (Nh, Nhat) the S-ROM basis.  Returns a CUDA tensor (B, nt) -- what the certification loop
+    (reference rom/hrom.py:504-626) collects per online parameter."""
+    from . import kernels
+
+    return kernels.rom_difference(uN, uN_srom, V_srom)
+
+
+def errors_summary_batch(err, index=None):
+    """Reductor.create_errors_summary (reference rom/base.py:154-163) for a (B, nt) error table on the device:
+    a pandas DataFrame with one row per parameter and the columns mean / median / max / min."""
+    import pandas as pd
+
+    from . import kernels
+
+    summ = kernels.errors_summary(err).cpu().numpy()
+    return pd.DataFrame(summ, columns=["mean", "median", "max", "min"], index=index)
+
+
 def time_average(ts, func):
     integrate = getattr(np, "trapezoid", None) or np.trapz
     return integrate(y=func, x=ts) / np.max(ts)

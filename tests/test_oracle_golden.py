@@ -87,3 +87,17 @@ def test_known_answer_properties():
     np.testing.assert_allclose(Q.T @ Q, np.eye(Q.shape[1]), atol=1e-13)
     assert abs(e[-1] - 1.0) < 1e-14
     assert np.isclose(orc.compute_rom_difference(np.ones(2), np.ones(3), np.eye(3)), 1 / np.sqrt(3))
+
+
+def test_certification_golden(golden):
+    """S-ROM estimator, RMS error and the per-parameter error summary against the reference's own functions."""
+    z = golden("certification")
+    for name in z["names"]:
+        V, uN, uS = z[f"{name}/V"], z[f"{name}/uN"], z[f"{name}/uS"]
+        np.testing.assert_allclose(orc.rom_difference_batch(uN, uS, V), z[f"{name}/err"], rtol=1e-13)
+        np.testing.assert_allclose(orc.errors_summary(z[f"{name}/err"]), z[f"{name}/summary"], rtol=1e-14)
+        B, nt, N = uN.shape
+        pad = np.zeros_like(uS)
+        pad[:, :, :N] = uN
+        rms = np.array([[orc.rms_error(uS[b, n], pad[b, n]) for n in range(nt)] for b in range(B)])
+        np.testing.assert_allclose(rms, z[f"{name}/rms"], rtol=1e-14)
