@@ -2,11 +2,10 @@
 //   rt_rom_difference_f64 : S-ROM estimator  err[b][n] = || V_srom (uN_srom - pad(uN)) ||_2 / sqrt(Nh)
 //                           for every (parameter, step)                       (utils.py:173-212)
 //   rt_errors_summary_f64 : mean / median / max / min over the steps of every parameter (rom/base.py:154-163)
-// The estimator is evaluated as the quadratic form sqrt(d^T G d / Nh), G = V_srom^T V_srom (Nhat x Nhat, from the
-// Gram kernel): the Nh-long linear combination of the reference is never formed.  2 Nhat^2 flop against
-// 8 (N + Nhat) bytes per (parameter, step) sits just above the FP64 ridge of a B200, so the rows go through
-// mma.sync.m8n8k4.f64: Y^T = G D^T with warp w owning the 8 rows [8w, 8w + 8) of G as A fragments in registers for
-// the whole kernel, 32 difference vectors per CTA iteration staged in shared memory as the B operand.
+// The estimator is evaluated as || R d ||_2 / sqrt(Nh) with R = chol(V_srom^T V_srom) (Nhat x Nhat, upper; the Gram
+// matrix comes from the Gram kernel): the Nh-long linear combination of the reference is never formed.  About
+// Nhat^2 flop against 8 (N + Nhat + 1) bytes per (parameter, step) is below the FP64 ridge of a B200: the kernel is an
+// HBM stream with the small triangular products on mma.sync.m8n8k4.f64.
 #include "common.cuh"
 
 namespace {
@@ -17,116 +16,129 @@ __device__ __forceinline__ void dmma884c(double& c0, double& c1, double a, doubl
                  : "d"(a), "d"(b));
 }
 
-constexpr int kRowsPerIter = 32;
-constexpr int kMaxK4 = 32;  // Nhat <= 128
-constexpr int kStages = 3;
-
-__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+// R = chol(G) (upper, R^T R = G; a non-positive pivot zeroes its row: semi-definite G from a rank-deficient basis),
+// written in A-fragment order  Rf[(nt * K4 + ks) * 32 + lane] = R[8 nt + lane / 4][kperm(ks, lane % 4)], zero padded to Np;
+// kperm(ks, q) = 8 (ks / 2) + 2 q + ks % 2: the k index is permuted (in R and in d alike) so that a lane's fragments of two
+// consecutive k-steps are ADJACENT columns of its row, i.e. one 16-byte load
+__global__ void __launch_bounds__(128) k_chol_frag(const double* __restrict__ G, int n, int Np, double* __restrict__ Rf) {
+    extern __shared__ __align__(16) double sm_a[];
+    const int ld = n + 1, t = threadIdx.x;
+    for (int e = t; e < n * n; e += 128) sm_a[(e / n) * ld + e % n] = G[e];
+    __syncthreads();
+    for (int j = 0; j < n; ++j) {
+        const double piv = sm_a[j * ld + j];
+        const double rd = piv > 0.0 ? 1.0 / sqrt(piv) : 0.0;
+        __syncthreads();
+        for (int k = j + t; k < n; k += 128) sm_a[j * ld + k] *= rd;  // row j of R (zero row if the pivot vanished)
+        __syncthreads();
+        for (int e = t; e < (n - j - 1) * (n - j - 1); e += 128) {
+            const int i = j + 1 + e / (n - j - 1), k = j + 1 + e % (n - j - 1);
+            if (k >= i) sm_a[i * ld + k] -= sm_a[j * ld + i] * sm_a[j * ld + k];
+        }
+        __syncthreads();
+    }
+    const int K4 = Np / 4;
+    for (int e = t; e < (Np / 8) * K4 * 32; e += 128) {
+        const int lane = e & 31, ks = (e >> 5) % K4, nt = (e >> 5) / K4;
+        const int i = 8 * nt + (lane >> 2), k = 8 * (ks >> 1) + 2 * (lane & 3) + (ks & 1);  // k-permutation, see below
+        Rf[e] = (i < n && k < n && k >= i) ? sm_a[i * ld + k] : 0.0;
+    }
 }
-__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
-}
 
-// grid: persistent; block: 32 * NT threads, NT = Nhat_pad / 8 warps.  Shared memory: kStages x {S tile, U tile}
-// (32 rows x LD each, pad columns zeroed once and never written again) + the partial sums.  The rows stream in by
-// cp.async, two stages ahead of the one being multiplied; d = S - U is formed when the fragments are read.
-__global__ void __launch_bounds__(512) k_rom_difference(const double* __restrict__ uN, const double* __restrict__ uS, int64_t R,
-                                                        int N, int Nhat, int Np, int LD, const double* __restrict__ G,
+// err[row] = || R d_row ||_2 / sqrt(Nh),  d = uS[row] - pad(uN[row]).  Every warp works alone on RT row tiles of 8 rows
+// per iteration: the difference vectors go from global memory straight into B fragments (lane (g8, q) holds
+// d[8 rt + g8][kperm(ks, q)]: full sectors, RT * K4 16-byte loads in flight per lane), R comes from shared
+// memory in A-fragment order (one conflict-free LDS.64 feeds RT DMMAs; only the k-tiles of the upper triangle are
+// visited), the squared entries of Y^T = R D^T are summed per row in registers and reduced over the 8 lanes that
+// share a row pair.  No block barrier after the set-up.
+template <int K4MAX, int RT>
+__global__ void __launch_bounds__(128) k_rom_difference(const double* __restrict__ uN, const double* __restrict__ uS, int64_t R,
+                                                        int N, int Nhat, int Np, const double* __restrict__ Rf,
                                                         double inv_Nh, double* __restrict__ err) {
     extern __shared__ __align__(16) double sm_c[];
-    const int tile = kRowsPerIter * LD;
-    double* part = sm_c + 2 * kStages * tile;  // NT x kRowsPerIter partial quadratic forms
-    const int t = threadIdx.x, lane = t & 31, w = t >> 5, NT = blockDim.x >> 5;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int g8 = lane >> 2, q = lane & 3;
-    const int K4 = Np >> 2;
-    for (int e = t; e < 2 * kStages * tile; e += blockDim.x) sm_c[e] = 0.0;
-    // A fragments of G rows [8w, 8w + 8): a[ks] = G[8w + g8][4 ks + q], zero beyond Nhat
-    double a[kMaxK4];
-#pragma unroll
-    for (int ks = 0; ks < kMaxK4; ++ks) {
-        const int i = 8 * w + g8, j = 4 * ks + q;
-        a[ks] = (ks < K4 && i < Nhat && j < Nhat) ? G[(int64_t)i * Nhat + j] : 0.0;
-    }
+    const int K4 = Np >> 2, NT8 = Np >> 3;
+    for (int e = t; e < NT8 * K4 * 32; e += blockDim.x) sm_c[e] = Rf[e];
     __syncthreads();
-    const bool wide = ((Nhat | N) & 1) == 0;
-    const int64_t stride = (int64_t)gridDim.x * kRowsPerIter;
-    auto issue = [&](int64_t r0, int stage) {
-        double* Ss = sm_c + (2 * stage) * tile;
-        double* Us = Ss + tile;
-        if (r0 < R) {
-            if (wide) {
-                const int cs = Nhat >> 1, cu = N >> 1;
-                for (int e = t; e < kRowsPerIter * cs; e += blockDim.x) {
-                    const int r = e / cs, c = e - r * cs;
-                    if (r0 + r < R) cp_async16(Ss + r * LD + 2 * c, uS + (r0 + r) * Nhat + 2 * c);
+    const bool wide = ((Nhat | N) & 1) == 0;  // 16-byte aligned rows
+    const int64_t rows_per_iter = 8 * RT;
+    const int64_t warp_id = (int64_t)blockIdx.x * (blockDim.x >> 5) + w, nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r0 = warp_id * rows_per_iter; r0 < R; r0 += nwarps * rows_per_iter) {
+        double fb[RT][K4MAX];
+        if (wide) {
+            // fragments (2j, q) and (2j + 1, q) are the adjacent columns 8 j + 2 q, + 1: one LDG.128 each for uS and uN
+            double2 us[RT][K4MAX / 2], un[RT][K4MAX / 2];
+#pragma unroll
+            for (int rt = 0; rt < RT; ++rt) {
+                const int64_t r = r0 + 8 * rt + g8;
+#pragma unroll
+                for (int j = 0; j < K4MAX / 2; ++j) {
+                    const int k = 8 * j + 2 * q;
+                    us[rt][j] = (2 * j < K4 && r < R && k < Nhat) ? __ldcs(reinterpret_cast<const double2*>(uS + r * Nhat + k))
+                                                                  : make_double2(0.0, 0.0);
+                    un[rt][j] = (2 * j < K4 && r < R && k < N) ? __ldcs(reinterpret_cast<const double2*>(uN + r * N + k))
+                                                               : make_double2(0.0, 0.0);
                 }
-                for (int e = t; e < kRowsPerIter * cu; e += blockDim.x) {
-                    const int r = e / cu, c = e - r * cu;
-                    if (r0 + r < R) cp_async16(Us + r * LD + 2 * c, uN + (r0 + r) * N + 2 * c);
+            }
+#pragma unroll
+            for (int rt = 0; rt < RT; ++rt)
+#pragma unroll
+                for (int j = 0; j < K4MAX / 2; ++j) {
+                    fb[rt][2 * j] = us[rt][j].x - un[rt][j].x;
+                    fb[rt][2 * j + 1] = us[rt][j].y - un[rt][j].y;
                 }
-            } else {
-                for (int e = t; e < kRowsPerIter * Nhat; e += blockDim.x) {
-                    const int r = e / Nhat, c = e - r * Nhat;
-                    if (r0 + r < R) cp_async8(Ss + r * LD + c, uS + (r0 + r) * Nhat + c);
-                }
-                for (int e = t; e < kRowsPerIter * N; e += blockDim.x) {
-                    const int r = e / N, c = e - r * N;
-                    if (r0 + r < R) cp_async8(Us + r * LD + c, uN + (r0 + r) * N + c);
+        } else {
+#pragma unroll
+            for (int rt = 0; rt < RT; ++rt) {
+                const int64_t r = r0 + 8 * rt + g8;
+#pragma unroll
+                for (int ks = 0; ks < K4MAX; ++ks) {
+                    const int k = 8 * (ks >> 1) + 2 * q + (ks & 1);
+                    double v = 0.0;
+                    if (ks < K4 && r < R && k < Nhat) {
+                        v = __ldcs(uS + r * Nhat + k);
+                        if (k < N) v -= __ldcs(uN + r * N + k);
+                    }
+                    fb[rt][ks] = v;
                 }
             }
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    int64_t r0 = (int64_t)blockIdx.x * kRowsPerIter;
+        double s0[RT], s1[RT];  // rows 8 rt + 2q and 8 rt + 2q + 1: sum over n of Y[row][n]^2 (this lane's n = 8 nt + g8)
 #pragma unroll
-    for (int s = 0; s < kStages - 1; ++s) issue(r0 + s * stride, s);
-    int stage = 0;
-    for (; r0 < R; r0 += stride) {
-        asm volatile("cp.async.wait_group %0;" ::"n"(kStages - 2) : "memory");
-        __syncthreads();  // this stage has landed for every thread; the stage consumed last iteration is free
-        issue(r0 + (kStages - 1) * stride, (stage + kStages - 1) % kStages);
-        const double* Ss = sm_c + (2 * stage) * tile;
-        const double* Us = Ss + tile;
-        double c[kRowsPerIter / 8][2];  // Y^T[8w + g8][rows 8 rt + 2q, + 1]: four independent accumulator chains
+        for (int rt = 0; rt < RT; ++rt) s0[rt] = s1[rt] = 0.0;
 #pragma unroll
-        for (int rt = 0; rt < kRowsPerIter / 8; ++rt) c[rt][0] = c[rt][1] = 0.0;
-        const int boff = g8 * LD + q;
+        for (int nt = 0; nt < K4MAX / 2; ++nt) {
+            if (nt < NT8) {
+                double c[RT][2];
 #pragma unroll
-        for (int ks = 0; ks < kMaxK4; ++ks) {
-            if (ks < K4) {
+                for (int rt = 0; rt < RT; ++rt) c[rt][0] = c[rt][1] = 0.0;
 #pragma unroll
-                for (int rt = 0; rt < kRowsPerIter / 8; ++rt) {
-                    const int o = boff + 8 * rt * LD + 4 * ks;
-                    dmma884c(c[rt][0], c[rt][1], a[ks], Ss[o] - Us[o]);
+                for (int ks = 2 * nt; ks < K4MAX; ++ks) {  // R is upper triangular: k-tiles left of the diagonal are zero
+                    if (ks < K4) {
+                        const double a = sm_c[(nt * K4 + ks) * 32 + lane];
+#pragma unroll
+                        for (int rt = 0; rt < RT; ++rt) dmma884c(c[rt][0], c[rt][1], a, fb[rt][ks]);
+                    }
                 }
+#pragma unroll
+                for (int rt = 0; rt < RT; ++rt) { s0[rt] = fma(c[rt][0], c[rt][0], s0[rt]); s1[rt] = fma(c[rt][1], c[rt][1], s1[rt]); }
             }
         }
-        const int n = 8 * w + g8;
 #pragma unroll
-        for (int rt = 0; rt < kRowsPerIter / 8; ++rt) {
-            const int o0 = (8 * rt + 2 * q) * LD + n, o1 = o0 + LD;
-            double p0 = c[rt][0] * (Ss[o0] - Us[o0]), p1 = c[rt][1] * (Ss[o1] - Us[o1]);
+        for (int rt = 0; rt < RT; ++rt) {
 #pragma unroll
             for (int o = 4; o < 32; o <<= 1) {
-                p0 += __shfl_xor_sync(0xffffffffu, p0, o);
-                p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+                s0[rt] += __shfl_xor_sync(0xffffffffu, s0[rt], o);
+                s1[rt] += __shfl_xor_sync(0xffffffffu, s1[rt], o);
             }
             if (g8 == 0) {
-                part[w * kRowsPerIter + 8 * rt + 2 * q] = p0;
-                part[w * kRowsPerIter + 8 * rt + 2 * q + 1] = p1;
+                const int64_t r = r0 + 8 * rt + 2 * q;
+                if (r < R) err[r] = sqrt(s0[rt] * inv_Nh);
+                if (r + 1 < R) err[r + 1] = sqrt(s1[rt] * inv_Nh);
             }
         }
-        __syncthreads();  // `part` is complete
-        if (t < kRowsPerIter && r0 + t < R) {
-            double s = 0.0;
-            for (int ww = 0; ww < NT; ++ww) s += part[ww * kRowsPerIter + t];  // fixed order: deterministic
-            err[r0 + t] = sqrt(fmax(s, 0.0) * inv_Nh);
-        }
-        // `part` is rewritten only after the next iteration's first barrier, which its 32 readers reach after reading it
-        stage = (stage + 1) % kStages;
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // one CTA per parameter: sort the nt errors in shared memory (bitonic, padded with +inf), then
@@ -152,13 +164,11 @@ __global__ void __launch_bounds__(256) k_errors_summary(const double* __restrict
     }
     for (int k = 2; k <= np2; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = t; i < np2; i += 256) {
-                const int l = i ^ j;
-                if (l > i) {
-                    const double x = v[i], y = v[l];
-                    const bool up = (i & k) == 0;
-                    if ((x > y) == up) { v[i] = y; v[l] = x; }
-                }
+            for (int pr = t; pr < (np2 >> 1); pr += 256) {  // one compare-exchange pair per thread and pass
+                const int i = ((pr & ~(j - 1)) << 1) | (pr & (j - 1)), l = i | j;
+                const double x = v[i], y = v[l];
+                const bool up = (i & k) == 0;
+                if ((x > y) == up) { v[i] = y; v[l] = x; }
             }
             __syncthreads();
         }
@@ -174,27 +184,42 @@ __global__ void __launch_bounds__(256) k_errors_summary(const double* __restrict
 
 }  // namespace
 
+template <int K4MAX, int RT>
+static int launch_rom_difference(rt_handle* h, const double* uN, const double* uS, int64_t R, int N, int Nhat, int Np,
+                                 const double* Rf, double inv_Nh, double* err, cudaStream_t st) {
+    auto fn = k_rom_difference<K4MAX, RT>;
+    const size_t smem = (size_t)Np * Np * sizeof(double);
+    if (smem > 48 * 1024) RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    RT_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    const int64_t want = ceil_div64(R, 8 * RT * 4);
+    const int64_t grid = want < (int64_t)h->sm_count * per_sm ? want : (int64_t)h->sm_count * per_sm;
+    fn<<<(unsigned)grid, 128, smem, st>>>(uN, uS, R, N, Nhat, Np, Rf, inv_Nh, err);
+    RT_LAUNCH_CHECK(h);
+    return RT_OK;
+}
+
 extern "C" int rt_rom_difference_f64(rt_handle* h, const double* uN, int64_t B, int64_t nt, int64_t N, const double* uN_srom,
                                      int64_t Nhat, const double* G, int64_t Nh, double* err, void* stream) {
     if (!h) return RT_EINVAL;
     RT_REQUIRE(h, uN && uN_srom && G && err);
     RT_REQUIRE(h, B >= 1 && nt >= 1 && N >= 1 && Nhat >= N && Nhat <= 128 && Nh >= 1);
     RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
     const int Np = (int)((Nhat + 7) / 8 * 8);
-    const int LD = (Np + 15) / 16 * 16 + 4;  // = 4 mod 16: conflict-free B-fragment reads
-    const int NT = Np / 8;
-    const size_t smem = ((size_t)2 * kStages * kRowsPerIter * LD + (size_t)NT * kRowsPerIter) * sizeof(double);
-    const int64_t R = B * nt;
-    const int64_t iters = ceil_div64(R, kRowsPerIter);
-    if (smem > 48 * 1024) RT_CUDA(h, cudaFuncSetAttribute(k_rom_difference, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int ctas_per_sm = 1;
-    RT_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k_rom_difference, 32 * NT, smem));
-    if (ctas_per_sm < 1) ctas_per_sm = 1;
-    const int64_t grid = iters < (int64_t)h->sm_count * ctas_per_sm ? iters : (int64_t)h->sm_count * ctas_per_sm;
-    k_rom_difference<<<(unsigned)grid, 32 * NT, smem, rt_stream(stream)>>>(uN, uN_srom, R, (int)N, (int)Nhat, Np, LD, G,
-                                                                          1.0 / (double)Nh, err);
+    void* rf;
+    int rc = rt_scratch(h, 3, (size_t)Np * Np * sizeof(double), &rf);
+    if (rc) return rc;
+    const size_t csmem = (size_t)Nhat * (Nhat + 1) * sizeof(double);
+    if (csmem > 48 * 1024) RT_CUDA(h, cudaFuncSetAttribute(k_chol_frag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem));
+    k_chol_frag<<<1, 128, csmem, st>>>(G, (int)Nhat, Np, (double*)rf);
     RT_LAUNCH_CHECK(h);
-    return RT_OK;
+    const int64_t R = B * nt;
+    if (Np <= 32) return launch_rom_difference<8, 2>(h, uN, uN_srom, R, (int)N, (int)Nhat, Np, (const double*)rf, 1.0 / (double)Nh, err, st);
+    if (Np <= 64) return launch_rom_difference<16, 2>(h, uN, uN_srom, R, (int)N, (int)Nhat, Np, (const double*)rf, 1.0 / (double)Nh, err, st);
+    if (Np <= 96) return launch_rom_difference<24, 1>(h, uN, uN_srom, R, (int)N, (int)Nhat, Np, (const double*)rf, 1.0 / (double)Nh, err, st);
+    return launch_rom_difference<32, 1>(h, uN, uN_srom, R, (int)N, (int)Nhat, Np, (const double*)rf, 1.0 / (double)Nh, err, st);
 }
 
 extern "C" int rt_errors_summary_f64(rt_handle* h, const double* err, int64_t B, int64_t nt, double* summary, void* stream) {
