@@ -313,8 +313,8 @@ def main():
                 "unit": "TFLOP/s", "frac": ach / peak,
                 "peak_source": "FP64 DMMA peak measured in this run (rt_fp64_peak_tflops; MEASURED_PEAKS.json has no fp64 entry)",
                 "avg_launch_ms": g_ms / g_n, "launches_timed": g_n, "share_of_step": g_ms / total_prof,
-                "traffic": 318.7e6,
-                "traffic_source": "dram bytes read+write per launch, ncu --set full, profiles/r1b_sweep_ncu.md",
+                "traffic": 1019.7e6 * chunk / 14208.0,
+                "traffic_source": "dram bytes read+write per launch (1019.7 MB at a 14208-parameter chunk, scaled to this chunk), ncu --set full, profiles/r1c_sweep_ncu.md",
                 "kernel_shares": {k: v[0] / total_prof for k, v in prof.items()}}
 
     # ---- certification leg: S-ROM estimator over every (parameter, step) of the last sweep
