@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--pod-rows", type=int, default=1_000_000)
     ap.add_argument("--pod-cols", type=int, default=4096)
     ap.add_argument("--skip-pod", action="store_true")
+    ap.add_argument("--c4-rows", type=int, default=200_000)
+    ap.add_argument("--c4-cols", type=int, default=2048)
     ap.add_argument("--skip-cpu", action="store_true")
     return ap.parse_args()
 
@@ -191,6 +193,62 @@ def pod_leg(a, torch, kernels, world, rank):
         "singular_values_head": [float(x) for x in s[:4]],
     }
     del S, G, W, Q
+    torch.cuda.empty_cache()
+    return res
+
+
+# ------------------------------------------------------------------------------- C4 leg (MDEIM offline chain)
+def c4_leg(a, torch, kernels, with_cpu):
+    """BASELINE.json configs[3]: POD (num = 128, not normalised) of 200,000 x 2048 matrix snapshots, then the greedy
+    point selection on the 200,000 x 128 collateral basis (deim/deim.py:517-561) -- the HBM-streaming kernel."""
+    from romtime_b200 import synthetic
+    from romtime_b200.rom import pod as podmod
+
+    nnz, n, m = a.c4_rows, a.c4_cols, 128
+    S = synthetic.mdeim_snapshots_device(nnz, n, seed=1004)
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    t_pod = None
+    for _ in range(3):
+        e0, e1 = ev(), ev()
+        e0.record()
+        Q, s, energy, VT, _ = podmod.orth_device(S, num=m, normalize=False)
+        e1.record()
+        torch.cuda.synchronize()
+        t_pod = e0.elapsed_time(e1) if t_pod is None else min(t_pod, e0.elapsed_time(e1))
+    del S
+    U = Q                                       # (nnz x m) column-major CUDA tensor
+    kernels.deim_greedy(U)
+    t_gr = None
+    for _ in range(5):
+        e0, e1 = ev(), ev()
+        e0.record()
+        dofs, PT_U = kernels.deim_greedy(U, sync=False)
+        e1.record()
+        torch.cuda.synchronize()
+        t_gr = e0.elapsed_time(e1) if t_gr is None else min(t_gr, e0.elapsed_time(e1))
+    alg = 8.0 * nnz * m * (m + 1) / 2           # SURVEY.md 8d: unblocked left-looking bytes
+    blk = 8.0 * nnz * m * (m / 8 + 1) / 2       # what the 8-column blocked kernel streams from HBM
+    hbm = hbm_peak_gbs()
+    res = {"shape": [nnz, n], "m": m, "pod_ms": t_pod, "pod_GBps_of_S": 8.0 * nnz * n / t_pod * 1e-6,
+           "sigma_m_over_sigma_1": float(s[m - 1] / s[0]), "greedy_ms": t_gr,
+           "greedy_algorithmic_GBps": alg / t_gr * 1e-6, "greedy_algorithmic_frac_of_hbm_peak": alg / t_gr * 1e-6 / hbm,
+           "greedy_blocked_traffic_GBps": blk / t_gr * 1e-6, "greedy_us_per_point": 1e3 * t_gr / m,
+           "hbm_peak_GBps": hbm, "unique_dofs": int(torch.unique(dofs).numel()),
+           "bound": "hbm by SURVEY.md 8d's algorithmic bytes (8 Nh m (m+1) / 2 = 13.2 GB -> 2.0 ms at peak); the blocked kernel "
+                    "streams 8x less and is bound by its m grid-wide arg-max exchanges"}
+    if with_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import romtime_oracle as orc_mod
+
+        Uh = U.cpu().numpy()
+        t0 = time.perf_counter()
+        ref_dofs = orc_mod.deim_greedy(Uh)
+        wall = time.perf_counter() - t0
+        res["cpu_greedy_ms"] = wall * 1e3
+        res["cpu_sample"] = f"oracle deim_greedy (deim/deim.py:517-561) on the same {nnz} x {m} basis, NumPy/OpenBLAS default threads"
+        res["indices_bit_exact"] = bool([int(d) for d in ref_dofs] == dofs.cpu().tolist())
+        res["PT_U_max_abs_diff"] = float(abs(PT_U.cpu().numpy() - Uh[ref_dofs, :]).max())  # P^T U is a row gather: exact
+    del U, Q
     torch.cuda.empty_cache()
     return res
 
@@ -365,6 +423,13 @@ def main():
         except Exception as exc:  # report, never hide
             pod = {"error": repr(exc)}
 
+    c4 = None
+    if not a.skip_pod and world == 1:
+        try:
+            c4 = c4_leg(a, torch, kernels, not a.skip_cpu)
+        except Exception as exc:  # report, never hide
+            c4 = {"error": repr(exc)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -373,7 +438,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Bl * 3 * 8) * world,
                     "d2h_bytes_per_step": int(Bl * nt * N * 8) * world},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_baseline,
-            "pod": pod, "certification": cert, "singular_solves": bad,
+            "pod": pod, "mdeim_c4": c4, "certification": cert, "singular_solves": bad,
         }
         emit(line, out_fd)
     if world > 1:
