@@ -377,6 +377,7 @@ def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=No
                 ev.record(side)
             copied[c % 2] = ev
         main.wait_stream(side)
+        side.synchronize()  # the history is in HOST memory: it must be complete when this returns
     return out_host, info
 
 
