@@ -115,12 +115,13 @@ __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& tm, 
     }
 }
 
-__device__ __forceinline__ void store_acc(const double (&acc)[MI][NI][2], double* C, int64_t ldc_m,
+template <int MI_>
+__device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI][2], double* C, int64_t ldc_m,
                                           int64_t ldc_n, int64_t M, int64_t N, int64_t m_base,
                                           int64_t n_base, int g, int tig, double alpha) {
     const bool vec = (ldc_n == 1) && ((ldc_m & 1) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
 #pragma unroll
-    for (int i = 0; i < MI; ++i) {
+    for (int i = 0; i < MI_; ++i) {
         const int64_t m = m_base + 8 * i + g;
         if (m >= M) continue;
 #pragma unroll
@@ -139,7 +140,9 @@ __device__ __forceinline__ void store_acc(const double (&acc)[MI][NI][2], double
     }
 }
 
-template <int AMAJOR, int BMAJOR>
+// NARROW (N <= 64, one column of tiles): the right half of the 128 x 128 tile would be all padding, so the eight consumer
+// warps split the rows instead (16 rows x 64 columns each) and half of the DMMAs disappear (the POD lift S W_r, r <= 64).
+template <int AMAJOR, int BMAJOR, bool NARROW>
 __global__ void __launch_bounds__(THREADS, 1)
 k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
     extern __shared__ unsigned char smem_raw[];
@@ -199,7 +202,8 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
     asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
     const int cw = warp - PRODUCER_WARPS;
     const int g = lane >> 2, tig = lane & 3;
-    const int wm0 = (cw / WARPS_N) * (MI * 8), wn0 = (cw % WARPS_N) * (NI * 8);
+    constexpr int MI_ = NARROW ? 2 : MI;
+    const int wm0 = NARROW ? cw * 16 : (cw / WARPS_N) * (MI * 8), wn0 = NARROW ? 0 : (cw % WARPS_N) * (NI * 8);
     // Fragment addresses as 32-bit shared-space offsets (LDS with immediate offsets instead of generic 64-bit
     // loads).  For k-step s the thread reads k index kq = 8*(tig>>1) + 2*((tig+s)&3) + (tig&1); in both majors rows
     // mn and mn + 16 are exactly 2048 bytes apart and the swizzle term only depends on (mn & 15, k), so two base
@@ -215,7 +219,7 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
         b_off[1][s] = TILE_BYTES + frag_off<BMAJOR>(wn0 + 8 + g, kq);
     }
 
-    double acc[MI][NI][2];
+    double acc[MI_][NI][2];
     int stage = 0;
     uint32_t phase = 0;
     for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
@@ -226,7 +230,7 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
         int kt1 = min(kt_total, kt0 + p.kt_per_split);
         if (p.kt_ranges) { const int2 r = p.kt_ranges[tm]; kt0 = r.x; kt1 = min(kt_total, r.y); }
 #pragma unroll
-        for (int i = 0; i < MI; ++i)
+        for (int i = 0; i < MI_; ++i)
 #pragma unroll
             for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
@@ -234,7 +238,7 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
             if (kt == p.hook_kt) {
                 store_acc(acc, p.C2, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, 1.0);
 #pragma unroll
-                for (int i = 0; i < MI; ++i)
+                for (int i = 0; i < MI_; ++i)
 #pragma unroll
                     for (int j = 0; j < NI; ++j) { acc[i][j][0] *= p.hook_scale; acc[i][j][1] *= p.hook_scale; }
             }
@@ -242,13 +246,13 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
             const uint32_t st_addr = smem_base + stage * STAGE_BYTES;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
-                double af[MI], bf[NI];
+                double af[MI_], bf[NI];
 #pragma unroll
-                for (int i = 0; i < MI; ++i) af[i] = lds_f64(st_addr + a_off[i & 1][s] + (uint32_t)(i >> 1) * 2048u);
+                for (int i = 0; i < MI_; ++i) af[i] = lds_f64(st_addr + a_off[i & 1][s] + (uint32_t)(i >> 1) * 2048u);
 #pragma unroll
                 for (int j = 0; j < NI; ++j) bf[j] = lds_f64(st_addr + b_off[j & 1][s] + (uint32_t)(j >> 1) * 2048u);
 #pragma unroll
-                for (int i = 0; i < MI; ++i)
+                for (int i = 0; i < MI_; ++i)
 #pragma unroll
                     for (int j = 0; j < NI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
             }
@@ -318,13 +322,19 @@ inline int make_map(rt_handle* h, const Operand& op, CUtensorMap* map) {
     return RT_OK;
 }
 
-template <int AMAJOR, int BMAJOR>
-inline int launch_t(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
-    auto fn = k_dgemm<AMAJOR, BMAJOR>;
+template <int AMAJOR, int BMAJOR, bool NARROW>
+inline int launch_n(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
+    auto fn = k_dgemm<AMAJOR, BMAJOR, NARROW>;
     RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     fn<<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
+}
+
+template <int AMAJOR, int BMAJOR>
+inline int launch_t(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
+    if (p.N <= 64 && !p.symmetric) return launch_n<AMAJOR, BMAJOR, true>(h, ma, mb, p, grid, st);
+    return launch_n<AMAJOR, BMAJOR, false>(h, ma, mb, p, grid, st);
 }
 
 // C = alpha * A B^T-style product of two "mn x k" operands.  `p` carries C, strides, split and hook

@@ -1,0 +1,98 @@
+"""The named configurations of BASELINE.json at (or near) their full sizes, checked through size-independent
+properties and oracle spot checks: C4 greedy at 200,000 x 128 against the oracle on the same basis, C5 sweep at
+65,536 parameters (spot parameters against the oracle, bitwise reproducibility, host-delivered history), C3 POD at
+4096 snapshots (orthonormality, singular values against a LAPACK eigensolve of the same Gram matrix, and the
+reconstruction identity S W_r = Q diag(s_r))."""
+import numpy as np
+import pytest
+
+import romtime_oracle as orc
+from romtime_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def test_c4_greedy_full_size_matches_oracle():
+    import torch
+
+    from romtime_b200 import kernels
+    from romtime_b200.rom.pod import orth_device
+
+    nnz, n, m = 200_000, 1024, 128
+    S = synthetic.mdeim_snapshots_device(nnz, n, seed=1004)
+    Q, s, energy, VT, _ = orth_device(S, num=m, normalize=False)
+    assert Q.shape == (nnz, m)
+    QtQ = (Q.t() @ Q - torch.eye(m, dtype=torch.float64, device=Q.device)).abs().max().item()
+    assert QtQ < 1e-6, QtQ          # Gram route: sigma_m / sigma_1 ~ 3e-4 costs about (sigma_1 / sigma_m)^2 eps
+    dofs, PT_U = kernels.deim_greedy(Q)
+    Uh = Q.cpu().numpy()
+    ref = orc.deim_greedy(Uh)
+    assert dofs.cpu().tolist() == ref
+    assert np.array_equal(PT_U.cpu().numpy(), Uh[ref, :])
+    assert len(set(ref)) == m
+    # every off-diagonal pair of the snapshots is duplicated bit for bit: a selected row that has a twin must be the
+    # lower index of the two (np.argmax keeps the first maximum)
+    A = Uh
+    for d in ref:
+        for twin in (d - 1, d + 1):
+            if 0 <= twin < nnz and np.array_equal(A[twin], A[d]):
+                assert d < twin, (d, twin)
+
+
+def test_c5_sweep_full_batch_properties():
+    import torch
+
+    from romtime_b200 import kernels
+
+    B, N, m, nt = 65536, 64, 128, 6
+    model = synthetic.make_piston_model(N=N, m=m, seed=1005)
+    mus = synthetic.sample_mus(B, seed=1005)
+    dm = kernels.DeviceRomModel(model)
+    u, info = kernels.online_sweep(dm, mus, nt, 1e-3, bdf=2, history=True)
+    assert u.shape == (B, nt, N)
+    assert not info.any().item()
+    assert torch.isfinite(u).all().item()
+    u2, _ = kernels.online_sweep(dm, mus, nt, 1e-3, bdf=2, history=True)
+    assert torch.equal(u, u2)                      # bitwise reproducible
+    hist, _ = kernels.online_sweep_to_host(dm, mus, nt, 1e-3, bdf=2)
+    assert np.array_equal(hist.numpy(), u.cpu().numpy())   # chunked + pipelined delivery changes nothing
+    # a permutation of the batch permutes the result: no dependence on the position in a chunk or tile
+    perm = np.random.default_rng(0).permutation(B)
+    up, _ = kernels.online_sweep(dm, mus[perm], nt, 1e-3, bdf=2, history=False)
+    assert np.array_equal(up.cpu().numpy(), u[:, -1, :].cpu().numpy()[perm])
+    uh = u.cpu().numpy()
+    for b in (0, 14207, 14208, 40000, B - 1):
+        ref = orc.rom_sweep(model, mus[b], nt, 1e-3, bdf2=True)
+        err = np.abs(uh[b].T - ref).max() / np.abs(ref).max()
+        assert err < 1e-10, (b, err)
+
+
+def test_c3_pod_properties_at_4096_snapshots():
+    import torch
+
+    from romtime_b200 import kernels
+    from romtime_b200.rom.pod import orth_device
+
+    Nh, n, k = 120_000, 4096, 256
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(1003)
+    sig = torch.pow(10.0, -torch.arange(k, dtype=torch.float64, device=dev) / 32.0)
+    S = (torch.randn((Nh, k), dtype=torch.float64, device=dev, generator=g) * sig) @ \
+        torch.randn((k, n), dtype=torch.float64, device=dev, generator=g)
+    S += 1e-13 * torch.randn((Nh, n), dtype=torch.float64, device=dev, generator=g)
+    Q, s, energy, VT, _ = orth_device(S, num=64, normalize=True)
+    assert Q.shape == (Nh, 64) and VT.shape == (64, n)
+    eye = torch.eye(64, dtype=torch.float64, device=dev)
+    assert (Q.t() @ Q - eye).abs().max().item() < 1e-9
+    assert (VT @ VT.t() - eye).abs().max().item() < 1e-10
+    assert np.all(np.diff(s[:k]) <= 0)
+    assert abs(energy[-1] - 1.0) < 1e-12
+    # singular values of the normalised snapshots = sqrt of the eigenvalues of the normalised Gram matrix (LAPACK)
+    G, cn = kernels.pod_gram(S, normalize=True)
+    lam = torch.linalg.eigvalsh(G).flip(0).clamp_min(0).sqrt().cpu().numpy()
+    assert np.abs(s[:64] - lam[:64]).max() / lam[0] < 1e-10
+    # reconstruction identity on the retained modes: (S D^-1) V_r = Q diag(s_r)
+    Sn = S / cn
+    lhs = Sn @ VT.t()
+    rhs = Q * torch.as_tensor(s[:64], device=dev)
+    assert (lhs - rhs).abs().max().item() / s[0] < 1e-10

@@ -56,7 +56,7 @@ def test_cross_gram(oa, ob):
 
 
 @pytest.mark.parametrize("order", ["C", "F"])
-@pytest.mark.parametrize("Nh,n,r", [(300, 24, 6), (5000, 130, 64), (4097, 64, 1), (999, 33, 33), (20000, 256, 200)])
+@pytest.mark.parametrize("Nh,n,r", [(300, 24, 6), (5000, 130, 64), (4097, 64, 1), (999, 33, 33), (20000, 256, 200), (40013, 200, 64), (40013, 96, 65)])
 def test_lift(Nh, n, r, order):
     from romtime_b200 import kernels
 
