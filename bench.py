@@ -194,6 +194,26 @@ def pod_leg(a, torch, kernels, world, rank):
     }
     del S, G, W, Q
     torch.cuda.empty_cache()
+    if rank == 0 and not a.skip_cpu:
+        # CPU baseline: the oracle's orth (rom/pod.py:7-62: column norms + LAPACK gesvd, all BLAS threads) on
+        # a bounded sample of the same family; the full-size figure is an O(Nh n^2) EXTRAPOLATION and is labelled as one
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import numpy as np
+        import romtime_oracle as orc_mod
+        from romtime_b200 import synthetic
+
+        nh_s, n_s = 16000, 1024
+        Ss = synthetic.pod_snapshots(nh_s, n_s, seed=1003)
+        t0 = time.perf_counter()
+        Qc, sc, _ = orc_mod.orth(Ss, num=64)
+        wall = time.perf_counter() - t0
+        res["cpu_orth_sample_ms"] = wall * 1e3
+        res["cpu_orth_sample"] = f"oracle orth (scipy gesvd) on {nh_s} x {n_s}, {os.cpu_count()} host cores, BLAS default threads"
+        res["cpu_orth_extrapolated_full_ms"] = wall * 1e3 * (Nh / nh_s) * (n / n_s) ** 2
+        res["cpu_orth_note"] = "extrapolated by Nh n^2 from the sample, not measured at full size"
+        # the device path on the same sample, for a like-for-like parity figure
+        Qd, sd, _, _, _ = podmod.orth_device(Ss, num=64)
+        res["sample_singular_values_max_rel"] = float(np.abs(sd[:64] - sc[:64]).max() / sc[0])
     return res
 
 
