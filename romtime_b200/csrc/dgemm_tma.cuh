@@ -52,6 +52,11 @@ struct Params {
     // optional block-sparse K: k-tile range [x, y) per M-tile (device pointer, tiles_m entries);
     // used for block-diagonal left operands (theta solve of all operators in one launch)
     const int2* kt_ranges;
+    // matvec form of the second output (when hook_w != nullptr): instead of storing the accumulators, every group of 64
+    // columns [64 r, 64 r + 64) is contracted with the row's vector  C2[m * hook_ldo + r] = sum_j acc(m, 64 r + j) *
+    // hook_w[m * hook_ldw + j]  (the online step's M(mu, t) w: M is never materialised)
+    const double* hook_w;
+    int64_t hook_ldw, hook_ldo;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -236,7 +241,37 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
 
         for (int kt = kt0; kt < kt1; ++kt) {
             if (kt == p.hook_kt) {
-                store_acc(acc, p.C2, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, 1.0);
+                if (p.hook_w) {
+                    const int r = 2 * tn + (wn0 >> 6);
+                    // two rows of accumulator tiles at a time: 16 loads in flight per lane (L2 latency is what this costs)
+#pragma unroll
+                    for (int i0 = 0; i0 < MI_; i0 += 2) {
+                        double2 wv[2][NI];
+#pragma unroll
+                        for (int ii = 0; ii < 2; ++ii) {
+                            const int64_t m = (int64_t)tm * BM + wm0 + 8 * (i0 + ii) + g;
+                            const double2* wrow = reinterpret_cast<const double2*>(p.hook_w + (m < p.M ? m : 0) * p.hook_ldw) + tig;
+#pragma unroll
+                            for (int j = 0; j < NI; ++j) wv[ii][j] = __ldg(wrow + 4 * j);
+                        }
+#pragma unroll
+                        for (int ii = 0; ii < 2; ++ii) {
+                            const int64_t m = (int64_t)tm * BM + wm0 + 8 * (i0 + ii) + g;
+                            double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                            for (int j = 0; j < NI; ++j) {
+                                s0 = fma(acc[i0 + ii][j][0], wv[ii][j].x, s0);
+                                s1 = fma(acc[i0 + ii][j][1], wv[ii][j].y, s1);
+                            }
+                            double sum = s0 + s1;
+                            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                            if (tig == 0 && m < p.M) p.C2[m * p.hook_ldo + r] = sum;
+                        }
+                    }
+                } else {
+                    store_acc(acc, p.C2, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, 1.0);
+                }
 #pragma unroll
                 for (int i = 0; i < MI_; ++i)
 #pragma unroll

@@ -736,6 +736,7 @@ __device__ __forceinline__ void gjs_update_col(GjsShared& sh, const double (&af)
 }
 
 __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* __restrict__ Kmat, const double* __restrict__ Mmat,
+                                                    const double* __restrict__ Mw,  // M w from the GEMM's matvec hook, or null
                                                     const double* __restrict__ From, const double* __restrict__ Wv, LuExtras ex,
                                                     double* __restrict__ Un, double* __restrict__ Unm1,
                                                     double* __restrict__ uN_out, int64_t out_stride_p, int64_t out_off,
@@ -755,7 +756,20 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
     if (t < 64) sh.pw[0][t] = t < N ? __ldg(Wv + p * pl.Npad + t) : 0.0;  // w staged in the (still unused) W buffer
     const int row = t >> 1, hp = t & 1;
     double s0 = 0.0, s1 = 0.0;
-    if (N == 64 && !Ma && !Ka) {
+    if (Mw) {
+        // M w already formed inside the assembly GEMM (N == 64, no dense extras): only K is loaded, two batches in flight
+        const double2* ktile = reinterpret_cast<const double2*>(Kp + g8 * 64 + 2 * q);  // + (8 rt) * 64 + 8 ct doubles
+        double2 b0[8], b1[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const int idx = w * 16 + i; b0[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const int idx = w * 16 + 8 + i; b1[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
+        if (hp == 0) s0 = __ldg(Mw + p * pl.Npad + row);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + lane] = b0[i];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lane] = b1[i];
+    } else if (N == 64 && !Ma && !Ka) {
         // fast path: four batches of eight 16-byte loads, two batches in flight
         const double2* mrow = reinterpret_cast<const double2*>(Mp + row * 64) + hp;
         const double2* ktile = reinterpret_cast<const double2*>(Kp + g8 * 64 + 2 * q);  // + (8 rt) * 64 + 8 ct doubles
@@ -944,7 +958,7 @@ struct Carver {
 struct SweepBuffers {
     double *basis_cat, *basis_rhs, *basis_til, *rhs_til, *Ccat, *Invcat, *Tpad;
     int2* kt_ranges;
-    double *Phi, *Ustar, *Wv, *Un, *Unm1, *TU, *F, *Kmat, *Mmat, *From;
+    double *Phi, *Ustar, *Wv, *Un, *Unm1, *TU, *F, *Kmat, *Mmat, *From, *Mw;
 };
 
 size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
@@ -968,6 +982,7 @@ size_t carve(Carver& c, const SweepPlan& pl, SweepBuffers& b) {
     b.Kmat = c.take<double>(Bcp * pl.ldk);
     b.Mmat = c.take<double>(Bcp * pl.ldk);
     b.From = c.take<double>(Bcp * pl.Npad);
+    b.Mw = c.take<double>(Bcp * pl.Npad);
     return setup_end;
 }
 
@@ -1009,8 +1024,15 @@ int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, cons
     return RT_OK;
 }
 
+// N == 64 without dense extras: the assembly GEMM contracts M(mu, t) with the history vector at its k-boundary instead of
+// storing M (466 MB per 14,208-parameter chunk never written nor read back)
+inline bool mw_in_gemm(const SweepPlan& pl, const LuExtras& ex) {
+    return pl.N == 64 && pl.ldk == 4096 && !ex.Kadd && !ex.Madd && pl.mpad[0] > 0 && pl.mpad[0] < pl.Qmat;
+}
+
 int launch_gj(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o, cudaStream_t st) {
-    k_gj_smem<<<pl.Bc, 128, 0, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off, o.info, o.step);
+    k_gj_smem<<<pl.Bc, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw_in_gemm(pl, ex) ? b.Mw : nullptr, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out,
+                                     o.stride_p, o.off, o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
@@ -1190,6 +1212,7 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
         dg::Params p = dg::default_params();
         p.C = b.Kmat; p.ldc_m = pl.ldk; p.ldc_n = 1;
         p.C2 = b.Mmat; p.hook_kt = pl.mpad[0] / 16; p.hook_scale = bdfc;
+        if (mw_in_gemm(pl, ex)) { p.C2 = b.Mw; p.hook_w = b.Wv; p.hook_ldw = pl.Npad; p.hook_ldo = pl.Npad; }
         if (p.hook_kt >= pl.Qmat / 16) {  // only a mass reductor: K = bdf M, no k-tile left to trigger the hook
             p.hook_kt = -1;
             p.alpha = 1.0;
