@@ -391,8 +391,8 @@ def main():
                 "unit": "TFLOP/s", "frac": ach / peak,
                 "peak_source": "FP64 DMMA peak measured in this run (rt_fp64_peak_tflops; MEASURED_PEAKS.json has no fp64 entry)",
                 "avg_launch_ms": g_ms / g_n, "launches_timed": g_n, "share_of_step": g_ms / total_prof,
-                "traffic": 533.5e6 * chunk / 14208.0,
-                "traffic_source": "dram bytes read+write per launch (533.5 MB at a 14208-parameter chunk, scaled to this chunk: K written once, M never stored), ncu --set full, profiles/r1h_sweep_ncu.md",
+                "traffic": 532.1e6 * chunk / 14208.0,
+                "traffic_source": "dram bytes read+write per launch (532.1 MB at a 14208-parameter chunk, scaled to this chunk: K written once, M never stored), ncu --set full, profiles/r1i_sweep_ncu.md",
                 "kernel_shares": {k: v[0] / total_prof for k, v in prof.items()}}
 
     # ---- certification leg: S-ROM estimator over every (parameter, step) of the last sweep

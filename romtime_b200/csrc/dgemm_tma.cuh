@@ -243,31 +243,29 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
             if (kt == p.hook_kt) {
                 if (p.hook_w) {
                     const int r = 2 * tn + (wn0 >> 6);
-                    // two rows of accumulator tiles at a time: 16 loads in flight per lane (L2 latency is what this costs)
+                    // one row of accumulator tiles at a time: its 8 loads are issued back to back (volatile asm keeps them
+                    // together; left to itself the compiler re-uses one register pair and serialises the L2 round trips)
 #pragma unroll
-                    for (int i0 = 0; i0 < MI_; i0 += 2) {
-                        double2 wv[2][NI];
+                    for (int i = 0; i < MI_; ++i) {
+                        const int64_t m = (int64_t)tm * BM + wm0 + 8 * i + g;
+                        const double* wrow = p.hook_w + (m < p.M ? m : 0) * p.hook_ldw + 2 * tig;
+                        double wx[NI], wy[NI];
 #pragma unroll
-                        for (int ii = 0; ii < 2; ++ii) {
-                            const int64_t m = (int64_t)tm * BM + wm0 + 8 * (i0 + ii) + g;
-                            const double2* wrow = reinterpret_cast<const double2*>(p.hook_w + (m < p.M ? m : 0) * p.hook_ldw) + tig;
+                        for (int j = 0; j < NI; ++j)
+                            asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(wx[j]), "=d"(wy[j]) : "l"(wrow + 8 * j));
+                        // all 16 values live at once: the FMAs may not start before the last load was issued
+                        asm volatile("" : "+d"(wx[0]), "+d"(wx[1]), "+d"(wx[2]), "+d"(wx[3]), "+d"(wx[4]), "+d"(wx[5]), "+d"(wx[6]), "+d"(wx[7]));
+                        asm volatile("" : "+d"(wy[0]), "+d"(wy[1]), "+d"(wy[2]), "+d"(wy[3]), "+d"(wy[4]), "+d"(wy[5]), "+d"(wy[6]), "+d"(wy[7]));
+                        double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-                            for (int j = 0; j < NI; ++j) wv[ii][j] = __ldg(wrow + 4 * j);
+                        for (int j = 0; j < NI; ++j) {
+                            s0 = fma(acc[i][j][0], wx[j], s0);
+                            s1 = fma(acc[i][j][1], wy[j], s1);
                         }
-#pragma unroll
-                        for (int ii = 0; ii < 2; ++ii) {
-                            const int64_t m = (int64_t)tm * BM + wm0 + 8 * (i0 + ii) + g;
-                            double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-                            for (int j = 0; j < NI; ++j) {
-                                s0 = fma(acc[i0 + ii][j][0], wv[ii][j].x, s0);
-                                s1 = fma(acc[i0 + ii][j][1], wv[ii][j].y, s1);
-                            }
-                            double sum = s0 + s1;
-                            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                            if (tig == 0 && m < p.M) p.C2[m * p.hook_ldo + r] = sum;
-                        }
+                        double sum = s0 + s1;
+                        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                        if (tig == 0 && m < p.M) p.C2[m * p.hook_ldo + r] = sum;
                     }
                 } else {
                     store_acc(acc, p.C2, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, 1.0);
