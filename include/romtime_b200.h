@@ -19,6 +19,14 @@
  *    LAPACK outputs) arrays are both accepted without a host-side copy.
  *  - indices are int64 (NumPy intp).
  *  - one handle per device; a handle is not thread-safe.
+ *
+ * Limits (the reference accepts any size; these are the sizes the kernels are built for -- a call outside
+ * them returns RT_EINVAL with the limit named in rt_last_error, the Python classes raise ValueError):
+ *  - reduced dimension N <= 128 (rt_online_*: the dense solve keeps one system per CTA in shared memory);
+ *  - collateral basis size m <= 160 for rt_invert_f64 / rt_deim_greedy_f64 (interpolation matrix in shared
+ *    memory), snapshots n <= 16384 for rt_sym_eig_f64, n <= 65535 for rt_pod_gram_f64;
+ *  - rt_errors_summary_f64: nt <= 16384;  rt_rom_difference_f64: N <= Nhat <= 128;
+ *  - rt_pod_batched_f64: n <= 256 snapshots per problem.
  */
 #ifndef ROMTIME_B200_H
 #define ROMTIME_B200_H
@@ -152,7 +160,10 @@ typedef struct {
     int32_t N;
     int32_t n_ops; /* 6 */
     int32_t evaluator;
-    int32_t reserved;
+    int32_t generation; /* 0: stage the model on every call.  Non-zero: a caller-chosen id, unique per set of device
+                         * tables; consecutive calls with a bitwise-identical rt_rom_model (same id, same pointers)
+                         * reuse the staged, PT_U^-1-folded operators kept in the handle.  Change the id whenever
+                         * the CONTENTS behind the pointers change. */
     rt_rom_operator ops[RT_MAX_OPS];
 } rt_rom_model;
 

@@ -207,6 +207,27 @@ def sampled_entries(model, op, mu, t, ustar=None):
     return f
 
 
+def online_step_entries(model, F_row, uN_n, uN_n1, dt, bdf_scheme, step):
+    """One implicit step of rom/rom.py:486-503 from a row of caller-supplied sampled entries (the f_local of every
+    reductor side by side in OPS order, deim/deim.py:437-438): theta solves (:491-492), reduced operators (:445),
+    K = bdf M + dt (A + C + N + N^) (rom/rom.py:906-907), b = M w + dt f (:919-925), dense solve.
+    ``uN_n1`` is the array of zeros on the first step (:456-460), bdf = 1.0 there (:481-483)."""
+    N = model["N"]
+    mats, off = {}, 0
+    for op in OPS:
+        m = model[op]["PT_U"].shape[0]
+        f = F_row[off:off + m]
+        off += m
+        if op == "rhs":
+            fg = interpolate(model[op]["basis_rom"], model[op]["PT_U"], f)
+        else:
+            mats[op] = interpolate_rom_matrix(model[op]["basis_rom"], model[op]["PT_U"], f, N)
+    bdf = 1.5 if (bdf_scheme == 2 and step > 0) else 1.0
+    K = bdf * mats["mass"] + dt * (mats["stiffness"] + mats["convection"] + mats["trilinear"] + mats["nonlinear_lifting"])
+    w = uN_n if bdf_scheme == 1 else 2.0 * uN_n - 0.5 * uN_n1
+    return np.linalg.solve(K, mats["mass"].dot(w) + dt * fg)
+
+
 def rom_sweep(model, mu, nt, dt, bdf2=True, solver="direct"):
     """RomConstructorNonlinear.solve for one parameter.  rom/rom.py:430-555 with
     assemble_system (:877-909) and assemble_system_rhs (:911-929).

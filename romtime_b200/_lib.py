@@ -39,7 +39,7 @@ class RomModel(ctypes.Structure):
         ("N", ctypes.c_int32),
         ("n_ops", ctypes.c_int32),
         ("evaluator", ctypes.c_int32),
-        ("reserved", ctypes.c_int32),
+        ("generation", ctypes.c_int32),
         ("ops", RomOperator * RT_MAX_OPS),
     ]
 

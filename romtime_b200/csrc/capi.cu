@@ -25,9 +25,12 @@ extern "C" int rt_create(int device, rt_handle** out) {
     return RT_OK;
 }
 
+void rt_online_release(rt_handle* h);  // online.cu
+
 extern "C" int rt_destroy(rt_handle* h) {
     if (!h) return RT_EINVAL;
     cudaSetDevice(h->device);
+    rt_online_release(h);
     for (int i = 0; i < rt_handle::kSlots; ++i)
         if (h->ws[i]) cudaFree(h->ws[i]);
     delete h;

@@ -21,7 +21,25 @@ struct rt_handle {
     double fp64_peak = 0.0;
     void* tma_encode = nullptr;  // cuTensorMapEncodeTiled, resolved lazily
     void* profile = nullptr;     // online-sweep profiler (online.cu)
+    void* sweep_cache = nullptr; // staged + folded online model of the last sweep / step (online.cu)
+    // largest dynamic shared-memory opt-in configured so far per kernel slot ON THIS DEVICE (the attribute is per
+    // device and per function: a process-wide flag would skip the opt-in on a second GPU or for a larger size)
+    static constexpr int kAttrSlots = 24;
+    int attr_smem[kAttrSlots] = {0};
 };
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (handle, kernel slot), re-issued when a larger size is needed
+template <typename F>
+inline int rt_ensure_smem(rt_handle* h, int slot, F fn, int bytes) {
+    if (h->attr_smem[slot] >= bytes) return RT_OK;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+        if (h) snprintf(h->err, sizeof(h->err), "cudaFuncSetAttribute(%d bytes, slot %d) failed: %s", bytes, slot, cudaGetErrorString(e));
+        return RT_ECUDA;
+    }
+    h->attr_smem[slot] = bytes;
+    return RT_OK;
+}
 
 inline int rt_fail(rt_handle* h, int code, const char* fmt, ...) {
     if (h) {

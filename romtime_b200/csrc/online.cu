@@ -998,11 +998,9 @@ int launch_lu(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const Lu
               cudaStream_t st) {
     const int ld = (pl.N + 1) | 1;
     const size_t smem = ((size_t)pl.N * ld + 2 * pl.N) * sizeof(double);
-    static bool attr_set[8] = {false};
-    if (!attr_set[R]) {
-        RT_CUDA(h, cudaFuncSetAttribute(k_lu_solve<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem > 48 * 1024 ? (int)smem : 48 * 1024));
-        attr_set[R] = true;
-    }
+    // per handle (= per device) and grown on demand: N = 70 then N = 96 share R = 3 but need 40 KB and 76 KB
+    int rc = rt_ensure_smem(h, R, k_lu_solve<R>, (int)smem);
+    if (rc) return rc;
     k_lu_solve<R><<<pl.Bc, kLuThreads, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
                                                    o.info, o.step);
     RT_LAUNCH_CHECK(h);
@@ -1013,11 +1011,8 @@ template <int NP>
 int launch_lu_reg(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o,
                   cudaStream_t st) {
     const size_t smem = ((size_t)NP * (NP + 2) + 2 * NP) * sizeof(double) + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
-        RT_CUDA(h, cudaFuncSetAttribute(k_lu_shift<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-        attr_set = true;
-    }
+    int rc = rt_ensure_smem(h, 8, k_lu_shift<NP>, 64 * 1024);
+    if (rc) return rc;
     k_lu_shift<NP><<<pl.Bc, NP, smem, st>>>(pl, b.Kmat, b.Mmat, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
                                             o.info, o.step);
     RT_LAUNCH_CHECK(h);
@@ -1046,9 +1041,33 @@ struct SweepCtx {
     int64_t chunk;
 };
 
+// The staged model of the last sweep / step, kept in the handle: a caller that marks its rt_rom_model with a non-zero
+// `generation` (unique per set of device tables) pays the table copies and the fold GEMM once, not once per call --
+// RomConstructor.solve drives rt_online_step_f64 once per time step with the same model.
+struct SweepCache {
+    bool valid = false;
+    rt_rom_model model;
+    bool need_evaluator = false;
+    int64_t B = 0;
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    cudaEvent_t ready = nullptr;
+    SweepCtx cx;
+};
+
 int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_evaluator, cudaStream_t st, SweepCtx& cx) {
     RT_REQUIRE(h, model->n_ops == kNOps);
-    RT_REQUIRE(h, model->N >= 1 && model->N <= 128);
+    if (model->N < 1 || model->N > 128)
+        return rt_fail(h, RT_EINVAL, "reduced dimension N = %d is outside the supported range 1..128", model->N);
+    if (!h->sweep_cache) h->sweep_cache = new SweepCache();
+    SweepCache* sc = (SweepCache*)h->sweep_cache;
+    if (sc->valid && model->generation != 0 && memcmp(&sc->model, model, sizeof(rt_rom_model)) == 0 &&
+        sc->need_evaluator == need_evaluator && sc->B == B && sc->ws == h->ws[8] && sc->ws_bytes == h->ws_bytes[8]) {
+        cx = sc->cx;
+        RT_CUDA(h, cudaStreamWaitEvent(st, sc->ready, 0));
+        return RT_OK;
+    }
+    sc->valid = false;
     RT_REQUIRE(h, model->evaluator == 0 || model->evaluator == 1);
     SweepPlan& pl = cx.pl;
     SweepBuffers& b = cx.b;
@@ -1154,6 +1173,17 @@ int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_ev
         int rc2 = dg::launch(h, oa, ob, p, st);
         if (rc2) return rc2;
     }
+    if (model->generation != 0) {
+        if (!sc->ready) RT_CUDA(h, cudaEventCreateWithFlags(&sc->ready, cudaEventDisableTiming));
+        RT_CUDA(h, cudaEventRecord(sc->ready, st));
+        sc->model = *model;
+        sc->need_evaluator = need_evaluator;
+        sc->B = B;
+        sc->ws = h->ws[8];
+        sc->ws_bytes = h->ws_bytes[8];
+        sc->cx = cx;
+        sc->valid = true;
+    }
     return RT_OK;
 }
 
@@ -1186,11 +1216,8 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
             ProfScope ps(prof, pa, 1, st);
             if (pl.N <= 64 && pl.m[kTril] <= 128) {
                 const size_t smem = ((size_t)128 * pl.Npad + 32 * (pl.Npad + 2)) * sizeof(double);
-                static bool attr_set = false;
-                if (!attr_set) {
-                    RT_CUDA(h, cudaFuncSetAttribute(k_tu, cudaFuncAttributeMaxDynamicSharedMemorySize, (128 * 64 + 32 * 66) * 8));
-                    attr_set = true;
-                }
+                rc = rt_ensure_smem(h, 9, k_tu, (128 * 64 + 32 * 66) * 8);
+                if (rc) return rc;
                 k_tu<<<(unsigned)ceil_div64(pl.Bc, 32), 256, smem, st>>>(pl, b.Tpad, b.Ustar, pl.m[kTril], b.TU);
                 RT_LAUNCH_CHECK(h);
             } else {
@@ -1231,11 +1258,8 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     if (pl.m[kRhs] > 0) {
         ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
         if (pl.N <= 64 && pl.mpad[kRhs] <= 128) {
-            static bool attr_set = false;
-            if (!attr_set) {
-                RT_CUDA(h, cudaFuncSetAttribute(k_forcing, cudaFuncAttributeMaxDynamicSharedMemorySize, (128 * 32 + 128 * 64) * 8));
-                attr_set = true;
-            }
+            rc = rt_ensure_smem(h, 10, k_forcing, (128 * 32 + 128 * 64) * 8);
+            if (rc) return rc;
             const size_t smem = ((size_t)128 * 32 + (size_t)pl.mpad[kRhs] * pl.Npad) * sizeof(double);
             k_forcing<<<(unsigned)ceil_div64(pl.Bc, 32), 256, smem, st>>>(pl, b.F + (size_t)pl.qoff[kRhs] * pl.Bcpad, b.rhs_til,
                                                                       pl.mpad[kRhs], b.From);
@@ -1336,6 +1360,22 @@ extern "C" int rt_online_step_f64(rt_handle* h, const rt_rom_model* model, const
         if (rc) return rc;
     }
     return RT_OK;
+}
+
+// called by rt_destroy (capi.cu): the handle-owned state of this translation unit
+void rt_online_release(rt_handle* h) {
+    if (h->sweep_cache) {
+        SweepCache* sc = (SweepCache*)h->sweep_cache;
+        if (sc->ready) cudaEventDestroy(sc->ready);
+        delete sc;
+        h->sweep_cache = nullptr;
+    }
+    if (h->profile) {
+        Profile* p = (Profile*)h->profile;
+        for (cudaEvent_t e : p->pool) cudaEventDestroy(e);
+        delete p;
+        h->profile = nullptr;
+    }
 }
 
 extern "C" int64_t rt_sweep_chunk(int64_t B, int N, int sm_count) {

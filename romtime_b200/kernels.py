@@ -63,6 +63,8 @@ def deim_greedy(U, sync=True):
     if Ud.dim() != 2:
         raise ValueError("basis must be a 2-D array (Nh x m)")
     Nh, m = Ud.shape
+    if m > 160:
+        raise ValueError(f"collateral basis size m = {m} exceeds the supported maximum 160 (include/romtime_b200.h, Limits)")
     dofs = torch.empty(m, dtype=torch.int64, device=Ud.device)
     PT_U = torch.empty((m, m), dtype=F64, device=Ud.device)
     info = torch.zeros(1, dtype=torch.int32, device=Ud.device)
@@ -198,6 +200,8 @@ def invert(A):
     """rt_invert_f64: inverse of a small dense matrix (m <= 160) by Gauss-Jordan with partial pivoting."""
     Ad = to_device(A).contiguous()
     m = Ad.shape[0]
+    if Ad.dim() != 2 or Ad.shape[1] != m or not 1 <= m <= DeviceRomModel.MAX_M:
+        raise ValueError(f"interpolation matrix must be square with 1 <= m <= {DeviceRomModel.MAX_M}, got {tuple(Ad.shape)}")
     Ainv = torch.empty_like(Ad)
     info = torch.zeros(1, dtype=torch.int32, device=Ad.device)
     h = handle(Ad.device.index)
@@ -244,8 +248,17 @@ class DeviceRomModel:
     basis_rom (column q contiguous), PT_U^-1 (computed once with rt_invert_f64) and, for the device
     evaluator of rt_online_sweep_f64, the tables C (m x 12) and T (m x N)."""
 
+    _generation = 0
+    MAX_N = 128   # include/romtime_b200.h "Limits"
+    MAX_M = 160
+
     def __init__(self, model, device=None):
         self.N = int(model["N"])
+        if not 1 <= self.N <= self.MAX_N:
+            raise ValueError(f"reduced dimension N = {self.N} is outside the supported range 1..{self.MAX_N} "
+                             "(the batched dense solve keeps one system per CTA in shared memory)")
+        # unique id of this set of device tables: lets the library keep the staged, folded operators between calls
+        DeviceRomModel._generation += 1
         self.evaluator = 0 if model.get("which", "rest") == "rest" else 1
         self._keep = []
         self.m = []
@@ -254,6 +267,7 @@ class DeviceRomModel:
         self.struct.N = self.N
         self.struct.n_ops = len(OPS)
         self.struct.evaluator = self.evaluator
+        self.struct.generation = DeviceRomModel._generation
         for i, name in enumerate(OPS):
             op = model.get(name)
             so = self.struct.ops[i]
@@ -266,6 +280,9 @@ class DeviceRomModel:
             rows_expected = self.N if name == "rhs" else self.N * self.N
             if basis.shape[0] != rows_expected:
                 raise ValueError(f"{name}: basis_rom has {basis.shape[0]} rows, expected {rows_expected}")
+            if basis.shape[1] > self.MAX_M:
+                raise ValueError(f"{name}: collateral basis size m = {basis.shape[1]} exceeds the supported maximum "
+                                 f"{self.MAX_M} (interpolation matrix inverse in shared memory)")
             bd = to_device(basis)
             inv = invert(np.ascontiguousarray(op["PT_U"], dtype=np.float64))
             Cd = Td = None

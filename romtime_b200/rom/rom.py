@@ -50,8 +50,6 @@ def _is_sparse_like(op):
 
 class RomConstructor(Reductor):
 
-    GMRES_OPTIONS = dict(atol=1e-10, tol=1e-10, maxiter=1e6)  # reference rom/rom.py:36 (documentation only)
-
     def __init__(self, fom, grid, name=None):
         super().__init__(grid=grid)
         self.fom = fom
@@ -291,10 +289,13 @@ class RomConstructor(Reductor):
         from .. import kernels
 
         slots = self._slot_reductors()
-        key = tuple(id(getattr(r, "basis_rom", None)) for v in slots.values() for r in (v if isinstance(v, list) else [v]))
-        key = (key, id(evaluator))
-        if self._dev_model is not None and self._dev_model[0] == key:
-            return self._dev_model[1]
+        # the cache entry KEEPS the objects it was built from and compares by identity (ids of freed objects are reused)
+        key = [getattr(r, "basis_rom", None) for v in slots.values() for r in (v if isinstance(v, list) else [v])]
+        key += [getattr(r, "PT_U", None) for v in slots.values() for r in (v if isinstance(v, list) else [v])]
+        key += [evaluator, self.basis]
+        hit = self._dev_model
+        if hit is not None and len(hit[0]) == len(key) and all(a is b for a, b in zip(hit[0], key)):
+            return hit[1]
         model = {"N": self.N, "which": evaluator.which if evaluator else "rest"}
         for name in _SLOTS:
             red = slots[name]
@@ -319,6 +320,12 @@ class RomConstructor(Reductor):
                 tab = evaluator.tables[name]
                 entry["C"], entry["T"] = tab["C"], tab.get("T")
             model[name] = entry
+        if all(model[name] is None for name in _SLOTS):
+            # pure Galerkin ROM (no hyper-reductor attached, the reference's default RomConstructor path through
+            # to_rom(fom.assemble_*), rom/rom.py:575-616): every operator arrives as a dense additive term of
+            # rt_online_step_f64; a one-mode zero mass operator keeps the device model non-empty
+            N = self.N
+            model["mass"] = {"basis_rom": np.zeros((N * N, 1)), "PT_U": np.eye(1)}
         dm = kernels.DeviceRomModel(model)
         self._dev_model = (key, dm)
         return dm
@@ -332,6 +339,8 @@ class RomConstructor(Reductor):
                     continue
                 extra = {"u_n": u_star} if name == "trilinear" else {}
                 parts.append(r._local_entries(mu, t, **extra))
+        if not parts:
+            return np.zeros(1)  # the dummy mass mode of a reductor-free model (_device_model)
         return np.concatenate(parts)
 
     def _dense_terms(self, mu, t, bdf, u_star):
@@ -439,8 +448,9 @@ class RomConstructor(Reductor):
         else:
             arr = np.asarray(mus, dtype=np.float64).reshape(-1, 3)
             mu_list = [{PistonParameters.A0: r[0], PistonParameters.OMEGA: r[1], PistonParameters.DELTA: r[2]} for r in arr]
-        for m in mu_list:
-            self.add_mu(mu=m, step=step)
+        self.mu_space[step].extend(mu_list)  # one operation: add_mu's list.index per parameter is O(B^2)
+        if mu_list:
+            self.mu = mu_list[-1]
         dm = self._device_model(evaluator)
         if to_host and history:
             out, info = kernels.online_sweep_to_host(dm, arr, nt, dt, bdf=bdf)

@@ -189,3 +189,45 @@ def test_sweep_is_bitwise_reproducible():
         assert torch.equal(first, again)
     ref = orc.rom_sweep(model, mus[5999], 6, 1e-3, bdf2=True)
     assert relerr(first[5999].cpu().numpy().T, ref) < 1e-10
+
+
+@pytest.mark.parametrize("sizes", [(70, 96), (100, 128), (65, 96, 70)])
+def test_dense_solve_growing_sizes_in_one_process(sizes):
+    """The shared-memory LU (N > 64) opts in to more than 48 KB of dynamic shared memory per reduced size: a larger
+    N after a smaller one of the same size class must raise the opt-in (round-1 bug: a per-class static flag)."""
+    from romtime_b200.rom.rom import _dense_solve
+
+    for N in sizes:
+        rng = np.random.default_rng(N)
+        K = rng.standard_normal((N, N)) + N * np.eye(N)
+        b = rng.standard_normal(N)
+        assert relerr(_dense_solve(K, b), np.linalg.solve(K, b)) < 1e-10
+
+
+def test_step_reuses_staged_model_and_sees_new_tables():
+    """rt_online_step_f64 keeps the staged model between calls (rt_rom_model.generation); a NEW DeviceRomModel --
+    even one whose tensors land on the same addresses -- must not hit the stale entry."""
+    import torch
+
+    from romtime_b200 import kernels
+
+    N, m, B = 16, 6, 5
+    outs = []
+    for seed in (31, 32):
+        model = synthetic.make_piston_model(N=N, m=m, seed=seed)
+        dm = kernels.DeviceRomModel(model)
+        rng = np.random.default_rng(5)
+        F = rng.standard_normal((B, dm.qsum))
+        Un = torch.zeros((B, N), dtype=torch.float64, device="cuda")
+        Unm1 = torch.zeros_like(Un)
+        info = torch.zeros(B, dtype=torch.int32, device="cuda")
+        for n in range(3):  # same model three times: steps 1, 2 run from the cached staging
+            kernels.online_step(dm, F, Un, Unm1, info, 1e-3, 2, n)
+        ref_u, ref_um1 = np.zeros((B, N)), np.zeros((B, N))
+        for n in range(3):
+            new = np.stack([orc.online_step_entries(model, F[b], ref_u[b], ref_um1[b], 1e-3, 2, n) for b in range(B)])
+            ref_um1, ref_u = ref_u, new
+        assert relerr(Un.cpu().numpy(), ref_u) < 1e-10
+        outs.append(Un.cpu().numpy())
+        del dm, Un, Unm1, info
+    assert relerr(outs[0], outs[1]) > 1e-3  # different models, different answers
