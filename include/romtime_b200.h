@@ -91,12 +91,30 @@ int rt_gram_finalize_f64(rt_handle* h, double* G, int64_t n, int normalize, doub
 int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int* info,
                    void* stream);
 
+/* Symmetric eigen-decomposition by PLAIN block Jacobi (no pivoted-Cholesky preconditioner): all n eigenpairs, W a
+ * product of plane rotations, rotation criterion |a_pq| > eps sqrt(a_pp a_qq).  On the Gram matrix H = Y^T Y of nearly
+ * orthogonal, arbitrarily graded columns every eigenvalue has a small RELATIVE error -- the rotation step of the
+ * one-sided (Hestenes) refinement that brings the method-of-snapshots POD to gesvd-level accuracy on every retained
+ * mode (rom/pod.py:38 resolves sigma_k to eps sigma_1; the Gram route alone only to eps sigma_1^2 / sigma_k).
+ * A (n x n row-major, ld n) is not modified; w descending; W row-major n x n, eigenvector k in column k;
+ * info (device int, may be NULL): sweeps used; defect (device double, may be NULL): max_{i != j} |a_ij| / sqrt(a_ii a_jj)
+ * of the input, i.e. how far the columns behind H are from orthogonal. */
+int rt_sym_eig_jacobi_f64(rt_handle* h, const double* A, int64_t n, double* w, double* W, int* info,
+                          double* defect, void* stream);
+
 /* Basis lift  Q = S Wr  (Nh x r): left singular vectors from the Gram eigenvectors,
  * Wr (n x r, row-major, leading dimension ldw) already scaled by 1/(sigma_k * colnorm_j).
  * Q is written with strides (q_stride_row, q_stride_col). */
 int rt_pod_lift_f64(rt_handle* h, const double* S, int64_t Nh, int64_t n, int64_t stride_row,
                     int64_t stride_col, const double* Wr, int64_t ldw, int64_t r, double* Q,
                     int64_t q_stride_row, int64_t q_stride_col, void* stream);
+
+/* Deflation step of the POD's second level: P (Nh x n row-major) holds Q (Q^T S D^-1) on entry (rt_gram_cross_f64 +
+ * rt_pod_lift_f64) and  S D^-1 - Q (Q^T S D^-1)  on exit -- what the delivered modes Q leave of the (column-normalised,
+ * colnorm != NULL) snapshots.  Its POD resolves the singular values the first Gram matrix cannot see
+ * (sigma_k < 4e-8 sigma_1; rom/pod.py:56 keeps every s > 1e-7 ABSOLUTE). */
+int rt_deflate_f64(rt_handle* h, const double* S, int64_t Nh, int64_t n, int64_t stride_row, int64_t stride_col,
+                   const double* colnorm, double* P, void* stream);
 
 /* ---------------------------------------------- DEIM greedy (deim/deim.py:517-561) ---- */
 /* Classic DEIM point selection on the collateral basis U (Nh x m):

@@ -34,6 +34,32 @@ __global__ void k_sym_scale(double* __restrict__ G, int64_t n, const double* __r
     }
 }
 
+// P[i][j] <- S[i][j] / cn[j] - P[i][j]   (P row-major Nh x n; S with element strides; cn may be null)
+__global__ void __launch_bounds__(256) k_deflate(const double* __restrict__ S, int64_t Nh, int64_t n, int64_t srow, int64_t scol,
+                                                 const double* __restrict__ cn, double* __restrict__ P) {
+    __shared__ double tile[32][33];
+    const int64_t i0 = (int64_t)blockIdx.y * 32, j0 = (int64_t)blockIdx.x * 32;
+    const bool col_fast = scol <= srow;  // read S along its fast axis, write P along its rows
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        if (col_fast) {
+            const int64_t i = i0 + r, j = j0 + threadIdx.x;
+            if (i < Nh && j < n) tile[r][threadIdx.x] = S[i * srow + j * scol];
+        } else {
+            const int64_t j = j0 + r, i = i0 + threadIdx.x;
+            if (i < Nh && j < n) tile[threadIdx.x][r] = S[i * srow + j * scol];
+        }
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t i = i0 + r, j = j0 + threadIdx.x;
+        if (i < Nh && j < n) {
+            double v = tile[r][threadIdx.x];
+            if (cn) v /= cn[j];
+            P[i * n + j] = v - P[i * n + j];
+        }
+    }
+}
+
 int gram_finalize(rt_handle* h, double* G, int64_t n, int normalize, double* colnorm, cudaStream_t st) {
     k_colnorm<<<(unsigned)ceil_div64(n, 256), 256, 0, st>>>(G, n, colnorm);
     RT_LAUNCH_CHECK(h);
@@ -99,4 +125,27 @@ extern "C" int rt_pod_lift_f64(rt_handle* h, const double* S, int64_t Nh, int64_
     dg::Params p = dg::default_params();
     p.C = Q; p.ldc_m = q_stride_row; p.ldc_n = q_stride_col;
     return dg::launch(h, a, b, p, st);
+}
+
+// Deflation step of the POD's second level (romtime_b200/rom/pod.py): with P = Q (Q^T S D^-1) already in `P`
+// (rt_gram_cross_f64 + rt_pod_lift_f64), P <- S D^-1 - P is what the delivered modes Q leave of the (column-normalised)
+// snapshots.  colnorm == NULL: D = I.  P is Nh x n row-major.
+extern "C" int rt_deflate_f64(rt_handle* h, const double* S, int64_t Nh, int64_t n, int64_t stride_row, int64_t stride_col,
+                              const double* colnorm, double* P, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, S && P && Nh >= 1 && n >= 1);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    const int64_t gy = ceil_div64(Nh, 32);
+    RT_REQUIRE(h, gy <= 2147483647LL && ceil_div64(n, 32) <= 65535);
+    // blockIdx.y is limited to 65535: rows go to grid.x when there are more than 2 M of them
+    dim3 grid((unsigned)ceil_div64(n, 32), (unsigned)(gy <= 65535 ? gy : 65535));
+    for (int64_t y0 = 0; y0 < gy; y0 += 65535) {
+        const int64_t rows0 = y0 * 32, rows = (Nh - rows0) < 65535LL * 32 ? (Nh - rows0) : 65535LL * 32;
+        dim3 g((unsigned)ceil_div64(n, 32), (unsigned)ceil_div64(rows, 32));
+        k_deflate<<<g, dim3(32, 8), 0, rt_stream(stream)>>>(S + rows0 * stride_row, rows, n, stride_row, stride_col, colnorm,
+                                                           P + rows0 * n);
+        RT_LAUNCH_CHECK(h);
+    }
+    (void)grid;
+    return RT_OK;
 }

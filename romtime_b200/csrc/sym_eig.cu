@@ -434,6 +434,28 @@ __global__ void k_mirror_upper(double* __restrict__ M, int64_t n, int64_t ld) {
     }
 }
 
+// out[0] = max_{i != j} |a_ij| / sqrt(a_ii a_jj): the departure from orthogonality of the columns whose Gram matrix A is
+// (one-sided Jacobi / Hestenes criterion).  Pairs with a non-positive diagonal product are skipped.  out is zeroed by the caller;
+// non-negative doubles order like their bit patterns, so the grid-wide maximum is one 64-bit atomicMax per CTA.
+__global__ void __launch_bounds__(256) k_scaled_defect(const double* __restrict__ A, int64_t n, int64_t lda, double* out) {
+    __shared__ double red[256];
+    const int64_t i = blockIdx.x;
+    const double aii = A[i * lda + i];
+    double v = 0.0;
+    for (int64_t j = threadIdx.x; j < n; j += blockDim.x) {
+        if (j == i) continue;
+        const double d = aii * A[j * lda + j];
+        if (d > 0.0) v = fmax(v, fabs(A[i * lda + j]) * rsqrt(d));
+    }
+    red[threadIdx.x] = v;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) red[threadIdx.x] = fmax(red[threadIdx.x], red[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(red[0]));
+}
+
 // X[:, c] *= 1/sqrt(lam_c) (zero column when lam_c <= 0);  w[c] = max(lam_c, 0)
 __global__ void k_scale_columns(double* __restrict__ X, int64_t r, int64_t ld, const double* __restrict__ lam,
                                 double* __restrict__ w) {
@@ -567,6 +589,31 @@ extern "C" int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, dou
         rc = dg::launch(h, opA, opB, p, st);
         if (rc) return rc;
     }
+    if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps, sizeof(int), cudaMemcpyHostToDevice, st));
+    RT_CUDA(h, cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+// Plain (un-preconditioned) block Jacobi on a symmetric matrix: ALL n eigenpairs, W a product of plane rotations
+// (orthogonal to working precision), relative rotation criterion |a_pq| > eps sqrt(a_pp a_qq) -- on a scaled diagonally
+// dominant matrix (the Gram matrix of nearly orthogonal, arbitrarily graded columns) every eigenvalue comes out with a
+// small RELATIVE error (Demmel-Veselic).  This is the rotation step of the Hestenes refinement behind orth
+// (romtime_b200/rom/pod.py): H = Y^T Y of the lifted modes Y = S W.  A (n x n, row-major, leading dimension n) is not
+// modified.  defect (device double, may be NULL) receives max |a_ij| / sqrt(a_ii a_jj) of the INPUT.
+extern "C" int rt_sym_eig_jacobi_f64(rt_handle* h, const double* A, int64_t n, double* w, double* W, int* info,
+                                     double* defect, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, A && w && W && n >= 1 && n <= 16384);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    if (defect) {
+        RT_CUDA(h, cudaMemsetAsync(defect, 0, sizeof(double), st));
+        k_scaled_defect<<<(unsigned)n, 256, 0, st>>>(A, n, n, defect);
+        RT_LAUNCH_CHECK(h);
+    }
+    int sweeps = 0;
+    int rc = jacobi_eig(h, A, n, n, w, W, n, 0.0, &sweeps, st);
+    if (rc) return rc;
     if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps, sizeof(int), cudaMemcpyHostToDevice, st));
     RT_CUDA(h, cudaStreamSynchronize(st));
     return RT_OK;

@@ -46,10 +46,16 @@ class DeviceBlockOps:
 
         return kernels.gram_cross(A, B)
 
-    def lift(self, S, W):  # S @ W, C-ordered so that it can be all-reduced in place
+    def lift(self, S, W, order="C"):  # S @ W, C-ordered by default so that it can be all-reduced in place
         from . import kernels
 
-        return kernels.pod_lift(S, W, order="C")
+        return kernels.pod_lift(S, W, order=order)
+
+    def jacobi(self, H):  # plain Jacobi on the Gram matrix of nearly orthogonal columns (Hestenes refinement)
+        from . import kernels
+
+        lam, X, _, defect = kernels.sym_eig_jacobi(H)
+        return lam, X, defect
 
     def finalize(self, G, normalize):
         from . import kernels
@@ -168,7 +174,7 @@ def orth_column_sharded(S_local, n, num=None, tol=None, normalize=True, block_op
 
     Returns ``(Q, s, energy, VT)``: Q (Nh x r) and VT (r x n) as tensors on this rank's device (Q is
     identical on every rank after the lift all-reduce), s / energy as NumPy arrays."""
-    from .rom.pod import _truncation
+    from .rom.pod import _energy, _guard_width, _truncation, refine_modes
 
     ops = block_ops or DeviceBlockOps()
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -182,23 +188,25 @@ def orth_column_sharded(S_local, n, num=None, tol=None, normalize=True, block_op
     k = min(Nh, n)
     w_host = w[:k].cpu().numpy()
     s = np.sqrt(np.maximum(w_host, 0.0))
-    lam = np.power(s, 2)
-    energy = np.cumsum(lam) / np.sum(lam)
-    keep = np.flatnonzero(_truncation(s, energy, num, tol))
-    r = len(keep)
+    nrank = int(np.count_nonzero(s > 0.0))
+    energy = _energy(s)
+    r = min(int(np.count_nonzero(_truncation(s, energy, num, tol))), nrank)
     if r == 0:
         return S_local.new_zeros((Nh, 0)), s, energy, W[:, :0].t()
-    idx = torch.as_tensor(keep, device=S_local.device)
-    Wk = W.index_select(1, idx)
-    sk = s[keep]
-    scale = torch.as_tensor(np.divide(1.0, sk, out=np.zeros_like(sk), where=sk > 0), device=S_local.device)
-    Wr = Wk * scale
-    if normalize:
-        Wr = Wr / cn[:, None]
-    Q = ops.lift(S_local, Wr[lo:hi].contiguous())
+    # lift of the retained + guard modes (this rank's columns' contribution), summed over the ranks; the Hestenes
+    # refinement (rom/pod.py) then runs replicated on the Nh x c result -- one level only on the sharded path
+    c = _guard_width(s, r, nrank)
+    Wc = W[:, :c].contiguous()
+    Wl = Wc / cn[:, None] if normalize else Wc
+    Y = ops.lift(S_local, Wl[lo:hi].contiguous())
     if world > 1:
-        dist.all_reduce(Q, op=dist.ReduceOp.SUM, group=group)
-    return Q, s, energy, Wk.t()
+        dist.all_reduce(Y, op=dist.ReduceOp.SUM, group=group)
+    sc, Q, VT, _, _ = refine_modes(Y, Wc, r, ops=ops)
+    s = s.copy()
+    s[:c] = sc
+    energy = _energy(s)
+    r = min(int(np.count_nonzero(_truncation(s, energy, num, tol))), Q.shape[1])
+    return Q[:, :r], s, energy, VT[:r]
 
 
 # ------------------------------------------------------------------------------- bench leg (N > 1)

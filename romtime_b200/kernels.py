@@ -155,6 +155,39 @@ def sym_eig(G):
     return w, W, int(info.item())
 
 
+def deflate(S, cn, Q):
+    """R = S D^-1 - Q (Q^T S D^-1)  (Nh x n, C-order): the snapshots with the delivered modes Q projected out
+    (rt_gram_cross_f64, rt_pod_lift_f64, rt_deflate_f64).  ``cn``: column norms (None: D = I)."""
+    Sd = to_device(S)
+    Nh, n = Sd.shape
+    T = gram_cross(Q, Sd)                       # r x n
+    if cn is not None:
+        T = T / cn[None, :]
+    P = pod_lift(Q, T.contiguous(), order="C")   # Nh x n
+    h = handle(Sd.device.index)
+    with torch.cuda.device(Sd.device):
+        rc = load_library().rt_deflate_f64(h, _ptr(Sd), Nh, n, Sd.stride(0), Sd.stride(1), _ptr(cn), _ptr(P), stream_ptr())
+    check(rc, h, "rt_deflate_f64")
+    return P
+
+
+def sym_eig_jacobi(H):
+    """rt_sym_eig_jacobi_f64: plain block Jacobi on the Gram matrix of nearly orthogonal columns.
+    Returns (w descending, W, sweeps, defect) -- defect = max |h_ij| / sqrt(h_ii h_jj) of the input."""
+    n = H.shape[0]
+    if not (H.is_contiguous() and H.dtype == F64):
+        H = H.contiguous().to(F64)
+    w = torch.empty(n, dtype=F64, device=H.device)
+    W = torch.empty((n, n), dtype=F64, device=H.device)
+    info = torch.zeros(1, dtype=torch.int32, device=H.device)
+    defect = torch.zeros(1, dtype=F64, device=H.device)
+    h = handle(H.device.index)
+    with torch.cuda.device(H.device):
+        rc = load_library().rt_sym_eig_jacobi_f64(h, _ptr(H), n, _ptr(w), _ptr(W), _ptr(info), _ptr(defect), stream_ptr())
+    check(rc, h, "rt_sym_eig_jacobi_f64")
+    return w, W, int(info.item()), float(defect.item())
+
+
 # ------------------------------------------------------------------ projections onto the reduced basis
 def project_vec(V, U):
     """rt_project_vec_f64: DEIM.project_basis, out (N x m) = V^T U."""

@@ -1,16 +1,26 @@
 """POD / ``orth`` on B200 -- drop-in for the reference's rom/pod.py:7-62.
 
-Same signature, same truncation rules, same return types (NumPy arrays on the host); the
-arithmetic is the method of snapshots on the device:
+Same signature, same truncation rules, same return types (NumPy arrays on the host).  The arithmetic is the method
+of snapshots followed by a one-sided (Hestenes) refinement of the modes that are returned:
 
-    G = S^T S (TMA-fed DMMA tiles, column norms = sqrt(diag G), normalisation D^-1 G D^-1 fused)
-    [multi-GPU: snapshot columns sharded, NCCL all-reduce of G -- see romtime_b200/distributed.py]
-    G = W diag(w) W^T  (block Jacobi),  s = sqrt(w),  VT = W^T
-    Q = S D^-1 W_r diag(1/s_r)          (lift GEMM)
+    G = S^T S                (TMA-fed DMMA tiles; column norms = sqrt(diag G), normalisation D^-1 G D^-1 fused)
+    [multi-GPU: snapshot columns sharded, NCCL all-reduce of G -- romtime_b200/distributed.py]
+    G = W diag(w) W^T        (pivoted Cholesky + block Jacobi),  s0 = sqrt(w)
+    Y = S D^-1 W_c           (lift of the c = retained + guard modes; columns ~ sigma_k u_k)
+    H = Y^T Y = X diag(lam) X^T   (plain Jacobi: H is the Gram matrix of NEARLY ORTHOGONAL graded columns, so its
+                                   entries carry errors relative to |y_i||y_j| and Jacobi resolves every lam_k to a
+                                   small RELATIVE error)
+    s_k = sqrt(lam_k),  Q = Y X_r diag(1/s_r),  VT = (W_c X_r)^T
 
-The Gram route squares the condition number: singular values below ~1e-8 * s[0] are noise (the
-reference's gesvd resolves them to ~1e-16 * s[0]).  Retained modes (s_k / s_0 >~ 1e-3) agree with
-gesvd to 1e-10 relative; see DESIGN.md "POD accuracy".
+The first Gram matrix squares the condition number: on its own it resolves sigma_k only to eps sigma_1^2 / sigma_k
+and a singular vector to eps (sigma_1 / sigma_k)^2.  The second, small Gram matrix is formed from vectors that are
+already orthogonal to ~eps (sigma_1/sigma_k)^2 <= 1e-3, which is all Demmel-Veselic need: after it every retained
+mode with sigma_k / sigma_1 >~ 1e-7 agrees with LAPACK gesvd (rom/pod.py:38) to the conditioning of the problem
+(values: eps sigma_1/sigma_k; vectors: eps sigma_1/gap).  The guard band keeps the directions just below the
+retained ones inside the rotation so that their leakage (eps (sigma_1/sigma_r)^2 sigma_j/sigma_r) stays below 1e-11.
+Modes below the Gram route's numerical rank (sigma_k < 4e-8 sigma_1) are only produced by the deflated second
+level (``_orth_level``: the same algorithm on S - Q Q^T S), which runs when the caller's truncation rule reaches
+that far (``num`` beyond the numerical rank, or the default 1e-7 ABSOLUTE floor).  See DESIGN.md "POD accuracy".
 """
 import numpy as np
 import torch
@@ -18,6 +28,10 @@ import torch
 from .. import kernels
 
 DROP_TOLERANCE = 1e-7  # rom/pod.py:4
+EPS = np.finfo(np.float64).eps
+GUARD_TAU = 1e-11      # admissible leakage of an excluded direction into a retained mode
+RANK_FLOOR = np.sqrt(8.0 * EPS)   # sigma_k / sigma_1 below which the first Gram matrix is noise (rt_sym_eig_f64's rank cut)
+DELIVER_FLOOR = (EPS * RANK_FLOOR / GUARD_TAU) ** (1.0 / 3.0)   # ~1e-4: see _resolve_level
 
 
 def _truncation(s, energy, num, tol):
@@ -33,41 +47,166 @@ def _truncation(s, energy, num, tol):
     return mask
 
 
-def orth_device(S, num=None, tol=None, normalize=True, allreduce=None):
-    """Device-resident POD. ``S`` is a CUDA tensor (Nh x n, any strides) or a NumPy array.
-    ``allreduce`` (optional callable) is applied to the raw Gram matrix before finalisation --
-    the hook used by the column/row-sharded multi-GPU path.
-    Returns (Q cuda Nh x r F-order, s numpy, energy numpy, VT cuda r x n, timings dict)."""
-    Sd = kernels.to_device(S)
-    Nh, n = Sd.shape
+def _energy(s):
+    lam = np.power(s, 2)
+    total = np.sum(lam)
+    return np.cumsum(lam) / total if total > 0 else np.ones_like(lam)
+
+
+def _guard_width(s0, r, rank):
+    """Candidate count c >= r: the modes j > r whose leakage into mode r, eps (s_1/s_r)^2 (s_j/s_r), exceeds
+    GUARD_TAU are rotated together with the retained ones."""
+    if r == 0 or r >= rank:
+        return min(r, rank)
+    amp = EPS * (s0[0] / s0[r - 1]) ** 2 / s0[r - 1]
+    c = r
+    while c < rank and amp * s0[c] > GUARD_TAU:
+        c += 1
+    return c
+
+
+class _KernelOps:
+    """The block operations of the refinement through libromtime_b200.so (the multi-GPU path and the CPU tests inject
+    their own: row-sharded Gram + all-reduce, test stand-ins)."""
+
+    @staticmethod
+    def gram(Y):
+        return kernels.pod_gram(Y, normalize=False)[0]
+
+    @staticmethod
+    def jacobi(H):
+        lam, X, _, defect = kernels.sym_eig_jacobi(H)
+        return lam, X, defect
+
+    @staticmethod
+    def lift(S, W, order="F"):
+        return kernels.pod_lift(S, W, order=order)
+
+
+def refine_modes(Y, Wc, n_keep, ops=None, max_passes=4):
+    """One-sided Jacobi (Hestenes) refinement of lifted modes.  ``Y`` (Nh x c) holds columns ~ sigma_k u_k that are
+    orthogonal up to the Gram route's error, ``Wc`` (n x c) the right vectors they were lifted with (or None).
+    Rotates until the columns are orthogonal to working precision; returns (s_c descending numpy, Q (Nh x n_keep,
+    orthonormal), VT (n_keep x n) or None, passes, first defect)."""
+    ops = ops or _KernelOps
+    c = Y.shape[1]
+    first_defect = None
+    for it in range(max_passes):
+        H = ops.gram(Y)
+        lam, X, defect = ops.jacobi(H)
+        if first_defect is None:
+            first_defect = defect
+        # kappa of the scaled Gram matrix <= (1 + c mu) / (1 - c mu): one rotation from a 10 %-defect is exact to working precision
+        if c * defect <= 0.1 or it == max_passes - 1:
+            break
+        Y = ops.lift(Y, X, order="F")
+        if Wc is not None:
+            Wc = ops.lift(Wc, X, order="C")
+    sc = np.sqrt(np.maximum(lam.cpu().numpy(), 0.0))
+    keep = min(n_keep, c)
+    inv = np.divide(1.0, sc[:keep], out=np.zeros(keep), where=sc[:keep] > 0)
+    Xr = (X[:, :keep] * torch.as_tensor(inv, device=Y.device)).contiguous()
+    Q = ops.lift(Y, Xr, order="F")
+    VT = None
+    if Wc is not None:
+        VT = ops.lift(Wc, X[:, :keep].contiguous(), order="C").t()
+    return sc, Q, VT, it + 1, first_defect
+
+
+def _resolve_level(A, normalize, allreduce, s_prefix, num, tol, k, Q_prev=None):
+    """One level of the POD: Gram -> eigensolve -> lift of the (still wanted + guard) modes -> Hestenes refinement.
+    ``s_prefix``: singular values already delivered by earlier levels (A is then the deflated remainder).
+    Returns (Q_new, VT_new, s_tail (k - len(s_prefix) values, refined where rotated), cn, info)."""
+    have = len(s_prefix)
+    Nh, n = A.shape
     if allreduce is None:
-        G, cn = kernels.pod_gram(Sd, normalize=normalize)
+        G, cn = kernels.pod_gram(A, normalize=normalize)
     else:
-        G, cn = kernels.pod_gram(Sd, normalize=False)
+        G, cn = kernels.pod_gram(A, normalize=False)
         allreduce(G)
         cn = kernels.gram_finalize(G, normalize=normalize)
     w, W, _ = kernels.sym_eig(G)
+    s_tail = np.sqrt(np.maximum(w[: k - have].cpu().numpy(), 0.0))
+    rank = int(np.count_nonzero(s_tail > 0.0))
+    info = {"rank_gram": rank, "candidates": 0, "passes": 0, "defect": 0.0}
+    empty = (torch.empty((0, Nh), dtype=torch.float64, device=A.device).t(), W[:, :0].t())
+
+    def wanted(tail):
+        full = np.concatenate([s_prefix, tail])
+        return int(np.count_nonzero(_truncation(full, _energy(full), num, tol))) - have
+
+    want = min(max(wanted(s_tail), 0), rank)
+    if want > 0 and have + rank < k:
+        # directions this Gram matrix cannot see (below RANK_FLOOR * s_tail[0]) cannot be put in the guard band: only modes
+        # they cannot contaminate (eps (s_1/s_r)^2 * floor / s_r <= GUARD_TAU, i.e. s_r >= ~1e-4 s_1) are delivered at
+        # this level, the rest by the next one (whose Gram matrix starts eight digits lower)
+        want = max(1, min(want, int(np.count_nonzero(s_tail >= DELIVER_FLOOR * s_tail[0]))))
+    if want == 0:
+        return empty[0], empty[1], s_tail, cn, info
+    c = _guard_width(s_tail, want, rank)
+    Wc = W[:, :c].contiguous()
+    Wl = (Wc / cn[:, None]).contiguous() if normalize else Wc   # rows scaled by 1/||S_j||: Y = (S D^-1) W_c
+    Y = kernels.pod_lift(A, Wl, order="F")
+    if Q_prev is not None and Q_prev.shape[1] > 0:
+        # the remainder was formed by a subtraction that leaves eps * sigma_1 of the delivered directions in it; relative
+        # to this level's modes that is not small, so the lifted columns are projected once more ("twice is enough")
+        Y = kernels.deflate(Y, None, Q_prev)
+    sc, Q, VT, passes, defect = refine_modes(Y, Wc, want)
+    s_tail = s_tail.copy()
+    s_tail[:c] = sc
+    info.update(candidates=c, passes=passes, defect=defect)
+    keep = min(max(wanted(s_tail), 0), Q.shape[1])   # the rule re-applied to the refined spectrum
+    return Q[:, :keep], VT[:keep], s_tail, cn, info
+
+
+MAX_LEVELS = 4
+
+
+def orth_device(S, num=None, tol=None, normalize=True, allreduce=None, deflate=True):
+    """Device-resident POD. ``S`` is a CUDA tensor (Nh x n, any strides) or a NumPy array.
+    ``allreduce`` (optional callable) is applied to the raw Gram matrix before finalisation --
+    the hook used by the row-sharded multi-GPU path.
+    Returns (Q cuda Nh x r F-order, s numpy, energy numpy, VT cuda r x n, info dict)."""
+    Sd = kernels.to_device(S)
+    Nh, n = Sd.shape
     k = min(Nh, n)
-    w_host = w[:k].cpu().numpy()
-    s = np.sqrt(np.maximum(w_host, 0.0))
-    eigenvalues = np.power(s, 2)
-    energy = np.cumsum(eigenvalues) / np.sum(eigenvalues)
-    mask = _truncation(s, energy, num, tol)
-    keep = np.flatnonzero(mask)
-    r = len(keep)
-    if r == 0:
-        Q = torch.empty((0, Nh), dtype=torch.float64, device=Sd.device).t()
-        return Q, s, energy, W[:, :0].t(), {}
-    idx = torch.as_tensor(keep, device=Sd.device)
-    Wk = W.index_select(1, idx)                      # n x r
-    sk = s[keep]
-    # modes below the rank-revealing tolerance come back as (0, zero vector): keep them zero
-    scale = torch.as_tensor(np.divide(1.0, sk, out=np.zeros_like(sk), where=sk > 0), device=Sd.device)
-    Wr = Wk * scale                                   # columns scaled by 1/sigma
-    if normalize:
-        Wr = Wr / cn[:, None]                         # rows scaled by 1/||S_j||
-    Q = kernels.pod_lift(Sd, Wr.contiguous(), order="F")
-    return Q, s, energy, Wk.t(), {}
+    default_rule = not tol and not num
+    A, norm = Sd, bool(normalize)
+    s = np.zeros(0)
+    Q = VT = cn1 = None
+    info = {"levels": 0}
+    for level in range(1, MAX_LEVELS + 1):
+        Qn, VTn, s_tail, cn, li = _resolve_level(A, norm, allreduce if level == 1 else None, s, num, tol, k, Q_prev=Q)
+        have = len(s)
+        s_all = np.concatenate([s, s_tail])
+        Q = Qn if Q is None else torch.cat([Q, Qn], dim=1)
+        VT = VTn if VT is None else torch.cat([VT, VTn], dim=0)
+        info["levels"] = level
+        if level == 1:
+            info.update(li)
+            cn1 = cn if normalize else None
+        r_total = int(np.count_nonzero(_truncation(s_all, _energy(s_all), num, tol)))
+        got = Q.shape[1]
+        # what this level could not see: everything below RANK_FLOOR * (its largest singular value)
+        floor_abs = RANK_FLOOR * (s_tail[0] if len(s_tail) else 0.0)
+        unseen = have + li["rank_gram"] < k
+        more = unseen and ((r_total > got) or (default_rule and floor_abs > DROP_TOLERANCE))
+        if not (deflate and allreduce is None and more and level < MAX_LEVELS and got > 0 and (Qn.shape[1] > 0 or level == 1)):
+            break
+        # deflate: R = S D^-1 - Q (Q^T S D^-1) keeps what the delivered modes leave; its POD resolves the next ~8 digits
+        A = kernels.deflate(Sd, cn1, Q)
+        norm = False
+        s = s_all[:got]
+    s = s_all
+    energy = _energy(s)
+    r_total = int(np.count_nonzero(_truncation(s, energy, num, tol)))
+    if r_total > Q.shape[1]:
+        pad = r_total - Q.shape[1]            # beyond every level's reach (pure rounding noise): keep the reference's shape
+        Q = torch.cat([Q, torch.zeros((Nh, pad), dtype=torch.float64, device=Sd.device)], dim=1)
+        VT = torch.cat([VT, torch.zeros((pad, n), dtype=torch.float64, device=Sd.device)], dim=0)
+    elif r_total < Q.shape[1]:
+        Q, VT = Q[:, :r_total], VT[:r_total]
+    return Q, s, energy, VT, info
 
 
 def orth(snapshots, num=None, tol=None, normalize=True, return_VT=False):

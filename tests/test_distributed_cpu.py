@@ -25,8 +25,14 @@ class TorchCpuBlockOps:
     def cross(self, A, B):
         return A.t() @ B
 
-    def lift(self, S, W):
+    def lift(self, S, W, order="C"):
         return (S @ W).contiguous()
+
+    def jacobi(self, H):
+        import pod_emulation
+
+        lam, X, _, defect = pod_emulation.sym_eig_jacobi(H)
+        return lam, X, defect
 
     def finalize(self, G, normalize):
         cn = torch.sqrt(torch.diagonal(G)).clone()
@@ -48,7 +54,7 @@ def _free_port():
 
 
 def _worker(rank, world, port, Nh, n, overlap, out_dir):
-    for p in (ROOT, os.path.join(ROOT, "oracle")):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
         if p not in sys.path:
             sys.path.insert(0, p)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -87,12 +93,12 @@ def test_column_sharded_pod_gloo(tmp_path, world, overlap):
     S = np.load(tmp_path / "S.npy")
     s = np.load(tmp_path / "s.npy")
     Qr, sr, _ = orc.orth(S, num=6)
-    assert np.max(np.abs(s[:6] - sr[:6]) / sr[:6]) < 1e-9
+    assert np.max(np.abs(s[:6] - sr[:6]) / sr[:6]) < 1e-10
     Qs = [np.load(tmp_path / f"Q{r}.npy") for r in range(world)]
     for Q in Qs[1:]:
         assert np.array_equal(Q, Qs[0]), "every rank must hold the same lifted basis"
     sign = np.sign(np.sum(Qs[0] * Qr, axis=0))
-    assert np.max(np.abs(Qs[0] * sign - Qr)) < 1e-8
+    assert np.max(np.abs(Qs[0] * sign - Qr)) < 1e-10
 
 
 def test_shard_range_partitions_exactly():
