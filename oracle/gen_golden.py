@@ -167,56 +167,7 @@ def gen_project_interp():
     print("project/interp: deim dofs", dofs[:5], "basis_rom", md.basis_rom.shape)
 
 
-def build_reference_rom(model, V, bdf, dt, nt, direct):
-    """Wire a reference RomConstructorNonlinear to the synthetic model."""
-    from romtime.deim.deim import DiscreteEmpiricalInterpolation
-    from romtime.deim.mdeim import MatrixDiscreteEmpiricalInterpolation
-    from romtime.deim.nonlinear import MatrixDiscreteEmpiricalInterpolationNonlinear
-    from romtime.rom.rom import RomConstructorNonlinear
-    import romtime_oracle as orc
-
-    N, m = model["N"], model["m"]
-    fom = ref_harness.DuckFom(Nh=V.shape[0], dt=dt, nt=nt, bdf_scheme=bdf)
-    rom = RomConstructorNonlinear(fom=fom, grid=None, name="golden")
-    rom.setup(rnd=0)
-    rom.basis = V
-    if direct:
-        rom.algebraic_solver = lambda A, b: (np.linalg.solve(A, b), 0)
-    Tfom = model["trilinear"]["T"] @ V.T  # (m, Nh): Tfom @ (V u) == T u
-
-    def feats(mu, t):
-        return orc.piston_features(mu["a0"], mu["omega"], mu["delta"], t, model["which"])
-
-    def make(op):
-        C = model[op]["C"]
-        if op == "trilinear":
-            def assemble(mu, t, entries=None, u_n=None):
-                phi = feats(mu, t)
-                return C @ phi + phi[11] * (Tfom @ u_n)
-            r = MatrixDiscreteEmpiricalInterpolationNonlinear(assemble=assemble, name=op)
-        elif op == "rhs":
-            def assemble(mu, t, entries=None):
-                return C @ feats(mu, t)
-            r = DiscreteEmpiricalInterpolation(assemble=assemble, name=op)
-        else:
-            def assemble(mu, t, entries=None):
-                return C @ feats(mu, t)
-            r = MatrixDiscreteEmpiricalInterpolation(assemble=assemble, name=op)
-        mm = model[op]["PT_U"].shape[0]
-        r.basis_fom = np.zeros((1, mm))  # only .shape[1] is read online (deim/deim.py:106-108)
-        r.basis_rom = model[op]["basis_rom"]
-        r.PT_U = model[op]["PT_U"]
-        r.dofs = [(k,) for k in range(mm)]
-        r.N_V = N
-        return r
-
-    rom.mdeim_Mh = make("mass")
-    rom.mdeim_Ah = make("stiffness")
-    rom.mdeim_Ch = make("convection")
-    rom.mdeim_Nh = make("trilinear")
-    rom.mdeim_Nh_hat = make("nonlinear_lifting")
-    rom.deim_fgh = make("rhs")
-    return rom
+build_reference_rom = ref_harness.build_reference_rom
 
 
 def gen_solve():

@@ -2,9 +2,10 @@
 /root/reference so that golden vectors can be generated in the build container.
 
 Nothing under romtime_b200/ may import this module.  /root/reference does not exist on
-the GPU box, so this file is only ever executed by oracle/gen_golden.py (which writes
-tests/golden/*.npz) and by the optional ``-m "not gpu"`` cross-check
-tests/test_oracle_vs_reference.py (skipped when /root/reference is absent).
+the GPU box; there the vendored copy under oracle/_ref (``make -C oracle``: a plain copy of the pure-Python
+package, git-ignored) is imported instead.  Used by oracle/gen_golden.py (writes tests/golden/*.npz), by the
+``-m "not gpu"`` cross-check tests/test_oracle_vs_reference.py (skipped when no reference tree is present) and by
+oracle/cpu_bench.py (the timed ``--impl reference`` arm of bench.py).
 
 The reference imports FEniCS / matplotlib / ujson at module import time
 (romtime/utils.py:4, romtime/rom/__init__.py:3, romtime/rom/rom.py:5-7) and uses three
@@ -18,7 +19,11 @@ import types
 
 import numpy as np
 
-REFERENCE_SRC = "/root/reference/src"
+HERE = os.path.dirname(os.path.abspath(__file__))
+# the mounted reference in the build container; on the GPU box the vendored copy that `make -C oracle` put under
+# oracle/_ref (git-ignored, travels with the snapshot) -- the package is pure Python, nothing is compiled
+_CANDIDATES = ("/root/reference/src", os.path.join(HERE, "_ref"))
+REFERENCE_SRC = next((c for c in _CANDIDATES if os.path.isdir(os.path.join(c, "romtime"))), _CANDIDATES[0])
 
 
 def reference_available():
@@ -158,3 +163,60 @@ class DuckFom:
         if self._lifting_fn is None:
             return _ArrayFunction(np.zeros(self._Nh))
         return _ArrayFunction(self._lifting_fn(mu, t))
+
+
+def build_reference_rom(model, V, bdf, dt, nt, direct):
+    """The reference's own RomConstructorNonlinear (rom/rom.py:739-974), unmodified, wired to a synthetic
+    hyper-reduced piston model (romtime_b200.synthetic.make_piston_model): its six reductors are the reference's own
+    DEIM / MDEIM / N-MDEIM classes with ``basis_rom`` / ``PT_U`` set directly and NumPy ``assemble`` callbacks in place
+    of FEniCS local assembly.  ``direct``: swap the algebraic-solver hook (rom/rom.py:414-425) for np.linalg.solve;
+    otherwise the stock GMRES (rom/rom.py:36) runs."""
+    load_reference()
+    from romtime.deim.deim import DiscreteEmpiricalInterpolation
+    from romtime.deim.mdeim import MatrixDiscreteEmpiricalInterpolation
+    from romtime.deim.nonlinear import MatrixDiscreteEmpiricalInterpolationNonlinear
+    from romtime.rom.rom import RomConstructorNonlinear
+    import romtime_oracle as orc
+
+    N = model["N"]
+    fom = DuckFom(Nh=V.shape[0], dt=dt, nt=nt, bdf_scheme=bdf)
+    rom = RomConstructorNonlinear(fom=fom, grid=None, name="golden")
+    rom.setup(rnd=0)
+    rom.basis = V
+    if direct:
+        rom.algebraic_solver = lambda A, b: (np.linalg.solve(A, b), 0)
+    Tfom = model["trilinear"]["T"] @ V.T  # (m, Nh): Tfom @ (V u) == T u
+
+    def feats(mu, t):
+        return orc.piston_features(mu["a0"], mu["omega"], mu["delta"], t, model["which"])
+
+    def make(op):
+        C = model[op]["C"]
+        if op == "trilinear":
+            def assemble(mu, t, entries=None, u_n=None):
+                phi = feats(mu, t)
+                return C @ phi + phi[11] * (Tfom @ u_n)
+            r = MatrixDiscreteEmpiricalInterpolationNonlinear(assemble=assemble, name=op)
+        elif op == "rhs":
+            def assemble(mu, t, entries=None):
+                return C @ feats(mu, t)
+            r = DiscreteEmpiricalInterpolation(assemble=assemble, name=op)
+        else:
+            def assemble(mu, t, entries=None):
+                return C @ feats(mu, t)
+            r = MatrixDiscreteEmpiricalInterpolation(assemble=assemble, name=op)
+        mm = model[op]["PT_U"].shape[0]
+        r.basis_fom = np.zeros((1, mm))  # only .shape[1] is read online (deim/deim.py:106-108)
+        r.basis_rom = model[op]["basis_rom"]
+        r.PT_U = model[op]["PT_U"]
+        r.dofs = [(k,) for k in range(mm)]
+        r.N_V = N
+        return r
+
+    rom.mdeim_Mh = make("mass")
+    rom.mdeim_Ah = make("stiffness")
+    rom.mdeim_Ch = make("convection")
+    rom.mdeim_Nh = make("trilinear")
+    rom.mdeim_Nh_hat = make("nonlinear_lifting")
+    rom.deim_fgh = make("rhs")
+    return rom

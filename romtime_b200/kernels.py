@@ -217,6 +217,8 @@ def project_mat(U, rows, cols, V):
         raise ValueError("rows/cols must have one entry per row of the collateral basis")
     if nnz and (rows_h.min() < 0 or cols_h.min() < 0 or rows_h.max() >= Nh or cols_h.max() >= Nh):
         raise ValueError("matrix topology does not fit the reduced basis (row/column index out of range)")
+    if nnz == 0 or m == 0:  # an operator without non-zeros (e.g. the trilinear term around u* = 0) projects to zero
+        return torch.zeros((m, N * N), dtype=F64, device=Vd.device).t()
     rd, cd = to_device(rows_h, torch.int64), to_device(cols_h, torch.int64)
     out = torch.empty((m, N * N), dtype=F64, device=Ud.device).t()
     h = handle(Ud.device.index)

@@ -132,7 +132,7 @@ def test_num_beyond_numerical_rank_is_orthonormal():
     from romtime_b200.rom.pod import orth
 
     Q, s, energy = orth(S, num=10, normalize=False)
-    assert Q.shape == (600, 10)
+    assert Q.shape == (S.shape[0], 10)
     assert np.max(np.abs(Q.T @ Q - np.eye(10))) < 1e-8
 
 
