@@ -603,75 +603,86 @@ __device__ __forceinline__ double2 gj_load2(const double* __restrict__ A, const 
 }
 
 // ------------------------------------------------------------------ blocked Gauss-Jordan on DMMA tiles (32 < N <= 64)
-// u = K^-1 b by Gauss-Jordan elimination with implicit partial pivoting, in 16 panels of 4 columns:
-//   panel:    4 pivot steps on the 64 x 4 panel held in registers (lane l: rows l and l + 32).  Arg-max over the
-//             rows that were not pivots yet (one redux.sync on a 32-bit key), the pivot record travels by shuffle,
-//             the pivot column is eliminated in EVERY other row.  The 4 steps compose to
-//                 X <- X - W Xraw[pivot rows]
-//             with a 64 x 4 matrix W accumulated next to the panel (3 DFMA per row and step).
-//   trailing: every live 8 x 8 tile gets ONE mma.sync.m8n8k4.f64:  C -= W_tile (8 x 4) * Xraw[pivot rows] (4 x 8).
-// After 16 panels the matrix is a row-permuted diagonal: x_k = rhs[piv_k] / pivot_k -- no triangular solves, no
-// stored factors.  The right-hand side b = M w + f rides along as a vector.
-// The padded 64 x 64 matrix lives in shared memory as 8 x 8 tiles in DMMA accumulator order (tile (rt, ct) =
-// 32 lanes x double2: one conflict-free LDS.128 / STS.128 per tile), so a CTA needs 80 registers per thread and
-// six parameters are resident per SM.  Four warps per parameter:
-//   warp 0 (panel warp): applies the pending update W_p to the tile column that holds panel p + 1, then factors
-//           panel p + 1 (no block barrier inside a panel) and updates the right-hand side;
-//   warps 1-3: apply W_p to the other live tile columns (look-ahead: this overlaps the next panel).
-// One block barrier per panel.  The raw pivot rows (B operand) and -W (A operand) are read straight from shared
-// memory; a tile column is always updated by ONE warp, which loads its B fragment before storing any tile.
+// u = K^-1 b by Gauss-Jordan elimination with implicit partial pivoting.  The padded 64 x 64 matrix lives in shared
+// memory as 8 x 8 tiles in DMMA accumulator order; it is processed in 8 PANELS of 8 columns (one tile column each),
+// every panel as two sub-panels of 4 columns.  The kernel is bound by the LATENCY of the one warp that factors a panel
+// (six parameters per SM is all the shared memory holds), so everything that is not a pivot step is kept off that
+// warp's dependent chain:
+//   pivot step: the 64 x 4 slab is in registers (a lane owns two rows).  Arg-max over the rows that were not pivots yet
+//              by ONE redux.sync on a 32-bit key; the pivot lane drops its record (4 doubles) into shared memory and all
+//              lanes read it back (56 cycles; eight or-reductions cost 124, eight shuffles 73); 1 / pivot by MUFU.RCP64H +
+//              a third-order correction beside the reduction; the pivot column is eliminated in EVERY other row.  The
+//              4 steps of a sub-panel compose to  X <- X - W Xraw[pivot rows]  with a 64 x 4 matrix W accumulated next
+//              to the slab (3 DFMA per row and step).
+//   panel:     sub-panel 1 gets the rank-4 update of sub-panel 0 in registers (the panel warp holds W1 and the slab);
+//              both (W1, g1), (W2, g2) are published as they are.
+//   trailing:  X <- X - W1 Xraw[g1] - W2 X'[g2],  X'[g2] = Xraw[g2] - W1[g2, :] Xraw[g1]  (the rows g2 after the first
+//              update, 4 DFMA per lane): two mma.sync.m8n8k4.f64 per 8 x 8 tile and panel, ONE LDS.128 + STS.128 per tile
+//              and panel -- half the shared-memory traffic of rank-4 updates.
+//   rhs:       b = M w + f rides along as a vector, updated by a trailing warp one panel behind.
+// After 8 panels the matrix is a row-permuted diagonal: x_c = rhs[row_c] / pivot_c -- no triangular solves, no stored
+// factors.  1 / pivot_c is parked in the (dead) pivot entry itself, the column a row was the pivot of in a byte array:
+// the solver state lives in shared memory, so the panel role can ROTATE over the four warps from panel to panel (a
+// warp's scheduler is warp id mod 4: a fixed panel warp puts the chains of all six resident parameters on one of the
+// four schedulers of the SM).  In iteration T one warp applies the pending update of panel T to tile column T + 1 and
+// factors it (look-ahead) while the other three update the remaining live tile columns; one block barrier per panel
+// plus a named barrier that protects the single W buffer.
+// Shared-memory layouts:
+//   tiles: element (i, j) in tile (i / 8, j / 8), slot ((i % 8) * 4 + (j % 8) / 2) ^ ((i / 8) & 3), component j & 1 -- a
+//          lane's accumulator slot XOR-ed by the tile row, so that the panel warp's row-wise LDS.128 of a quarter warp
+//          (rows of four different tile rows) hit eight distinct 16-byte bank groups; tile accesses stay conflict-free;
+//   nw[h]: -W of sub-panel h, element (row, k) at k * 68 + row: conflict-free for the panel warp's row-wise STS.64 and
+//          for the A-fragment LDS.64 of the trailing warps (lane (g8, q) reads q * 68 + 8 rt + g8).
+constexpr int kGjLdw = 68;
 struct GjsShared {
-    double2 tiles[64 * 32];  // tile (rt, ct) at (rt * 8 + ct) * 32, lane-major
-    double pw[2][64 * 4];    // -W of panel p (parity p & 1), A-fragment order (row * 4 + k)
+    double2 tiles[64 * 32];
+    double nw[2][4 * kGjLdw];
     double rhs[64];
-    int gr[2][4];            // pivot rows of panel p (parity p & 1)
+    double2 rec[4][2];        // pivot record of step J of the running sub-panel
+    int gr[8];                // pivot rows of the published panel (g1, g2)
+    unsigned char colof[64];  // column that row i was the pivot of (0xff: none yet)
 };
 
-struct GjsPanelState {
-    bool done0, done1, sing;
-    double rd0, rd1;  // lane l: reciprocal pivots of columns l and l + 32
-    int pv0, pv1;     //         and their pivot rows
-};
+// offset (in doubles, tile column 0) of element (i, 8 ct + n) -- add 64 ct
+__device__ __forceinline__ int gjs_rowoff(int i, int n) {
+    const int rt = i >> 3;
+    return ((rt * 256 + ((((i & 7) << 2) | (n >> 1)) ^ (rt & 3))) << 1) | (n & 1);
+}
 
-#ifndef GJS_REDUX_BROADCAST
-#define GJS_REDUX_BROADCAST 1
-#endif
+// 1 / x to ~1 ulp: MUFU.RCP64H seed (20 bits) and one third-order step x0 (1 + e + e^2), e = 1 - x x0 -- three dependent
+// DFMA (40 cycles) instead of the rcp.rn.f64 sequence (76).  x = 0 (or subnormal) gives NaN / inf.
+__device__ __forceinline__ double gjs_rcp(double x) {
+    double x0;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x0) : "d"(x));
+    const double e = fma(-x, x0, 1.0);
+    const double p = fma(e, e, e);
+    return fma(x0, p, x0);
+}
+
+// one pivot step of a sub-panel; the lane owns rows row0 and row0 + 32 (a0 / a1: slab, w0 / w1: multipliers).
+// rb0 / rb1 = 64 | (63 - row): the 7 low key bits (candidate flag, row); cand0 / cand1 = all ones while the row has not been a pivot.
 template <int J>
-__device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4], GjsPanelState& ps,
-                                         int (&gr)[4], int col, int lane) {
-    // key: high word of |a_J|, 7 low bits = (candidate flag, 63 - row): the pivot is within 2^-13 of the column maximum
-    const unsigned k0 = ps.done0 ? 0u : (((unsigned)__double2hiint(a0[J]) & 0x7fffff80u) | 64u | (unsigned)(63 - lane));
-    const unsigned k1 = ps.done1 ? 0u : (((unsigned)__double2hiint(a1[J]) & 0x7fffff80u) | 64u | (unsigned)(31 - lane));
+__device__ __forceinline__ void gjs_step(GjsShared& sh, double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4],
+                                         unsigned& cand0, unsigned& cand1, int (&gr)[4], unsigned rb0, unsigned rb1) {
+    // key: high word of |a_J| over the row bits: the pivot is within 2^-13 of the column maximum, the lowest row wins ties
+    const unsigned k0 = (((unsigned)__double2hiint(a0[J]) & 0x7fffff80u) | rb0) & cand0;
+    const unsigned k1 = (((unsigned)__double2hiint(a1[J]) & 0x7fffff80u) | rb1) & cand1;
     const bool sel = k1 > k0;
     const unsigned mx = __reduce_max_sync(0xffffffffu, sel ? k1 : k0);
-    // reciprocal of the lane's own candidate, issued AFTER the reduction so that its dependent chain runs beside it
-    double rinv_loc;
-    asm volatile("rcp.rn.f64 %0, %1;" : "=d"(rinv_loc) : "d"(sel ? a1[J] : a0[J]));
+    // reciprocal of the lane's own candidate: independent of the reduction, its chain runs beside it
+    const double rinv_loc = gjs_rcp(sel ? a1[J] : a0[J]);
     double rec[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) rec[j] = j < J ? (sel ? w1[j] : w0[j]) : (j == J ? rinv_loc : (sel ? a1[j] : a0[j]));
-    const int g = 63 - (int)(mx & 63u);
-    const int src = g & 31;
-    double r[4];
-#if GJS_REDUX_BROADCAST
-    // broadcast by or-reduction: redux.sync does not queue behind the tile traffic of the trailing warps in the
-    // shared-memory pipe the way shuffles do
-    {
-        const bool is_src = lane == src;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const unsigned lo = __reduce_or_sync(0xffffffffu, is_src ? (unsigned)__double2loint(rec[j]) : 0u);
-            const unsigned hi = __reduce_or_sync(0xffffffffu, is_src ? (unsigned)__double2hiint(rec[j]) : 0u);
-            r[j] = __hiloint2double((int)hi, (int)lo);
-        }
+    const bool me0 = ((mx ^ rb0) & 127u) == 0u, me1 = ((mx ^ rb1) & 127u) == 0u;
+    if (me0 | me1) {
+        sh.rec[J][0] = make_double2(rec[0], rec[1]);
+        sh.rec[J][1] = make_double2(rec[2], rec[3]);
     }
-#else
-#pragma unroll
-    for (int j = 0; j < 4; ++j) r[j] = __shfl_sync(0xffffffffu, rec[j], src);
-#endif
-    gr[J] = g;
-    const bool me0 = g == lane, me1 = g == lane + 32;
-    if ((me0 && a0[J] == 0.0) || (me1 && a1[J] == 0.0)) ps.sing = true;
+    __syncwarp();
+    const double2 ra = sh.rec[J][0], rb = sh.rec[J][1];
+    const double r[4] = {ra.x, ra.y, rb.x, rb.y};
+    gr[J] = 63 - (int)(mx & 63u);
     const double l0 = me0 ? 0.0 : a0[J] * r[J];
     const double l1 = me1 ? 0.0 : a1[J] * r[J];
 #pragma unroll
@@ -680,59 +691,159 @@ __device__ __forceinline__ void gjs_step(double (&a0)[4], double (&a1)[4], doubl
     for (int j = 0; j < J; ++j) { w0[j] = fma(-l0, r[j], w0[j]); w1[j] = fma(-l1, r[j], w1[j]); }
     w0[J] = l0;
     w1[J] = l1;
-    ps.done0 |= me0;
-    ps.done1 |= me1;
-    if (lane == (col & 31)) {
-        if (col < 32) { ps.rd0 = r[J]; ps.pv0 = g; }
-        else { ps.rd1 = r[J]; ps.pv1 = g; }
-    }
+    cand0 = me0 ? 0u : cand0;
+    cand1 = me1 ? 0u : cand1;
 }
 
-// warp 0: factor panel pn (columns 4 pn .. 4 pn + 3); publishes -W and the pivot rows under parity pn & 1
-__device__ __forceinline__ void gjs_factor(GjsShared& sh, GjsPanelState& ps, int pn, int lane) {
-    const int ct = pn >> 1, h = pn & 1, par = pn & 1;
-    double a0[4], a1[4], w0[4] = {0.0, 0.0, 0.0, 0.0}, w1[4] = {0.0, 0.0, 0.0, 0.0};
+// 4 pivot steps on the slab (a0, a1) = sub-panel h of tile column T: W in (w0, w1), pivot rows gr; publishes -W, the pivot
+// rows, 1 / pivot (parked in the pivot entry) and the rows' columns
+__device__ __forceinline__ void gjs_subpanel(GjsShared& sh, int T, int h, double (&a0)[4], double (&a1)[4], double (&w0)[4],
+                                             double (&w1)[4], int (&gr)[4], unsigned& cand0, unsigned& cand1, int row0, int lane,
+                                             bool guard, int* __restrict__ info_p, int step) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { w0[j] = 0.0; w1[j] = 0.0; }
+    const unsigned rb0 = 64u | (unsigned)(63 - row0), rb1 = 64u | (unsigned)(31 - row0);
+    gjs_step<0>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
+    gjs_step<1>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
+    gjs_step<2>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
+    gjs_step<3>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
+    // the other warps have read what they need of the previous panel: sh.nw / sh.gr may be overwritten
+    if (guard) asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { sh.nw[h][k * kGjLdw + row0] = -w0[k]; sh.nw[h][k * kGjLdw + row0 + 32] = -w1[k]; }
+    if (lane < 4) {
+        // lane J records pivot J.  1 / pivot is entry J of step J's record, still in the record buffer; it is parked in the
+        // pivot entry (g, col) -- the column is finished, nobody reads it again as a matrix entry --, the column in colof[g];
+        // a vanished pivot (1 / pivot not finite) flags the parameter
+        const int g = lane == 0 ? gr[0] : (lane == 1 ? gr[1] : (lane == 2 ? gr[2] : gr[3]));
+        const double rv = reinterpret_cast<const double*>(sh.rec)[5 * lane];
+        sh.gr[4 * h + lane] = g;
+        reinterpret_cast<double*>(sh.tiles)[64 * T + gjs_rowoff(g, 4 * h + lane)] = rv;
+        sh.colof[g] = (unsigned char)(8 * T + 4 * h + lane);
+        if (!(fabs(rv) < 1.7976931348623157e308)) atomicCAS(info_p + blockIdx.x, 0, step + 1);
+    }
+    __syncwarp();  // the record buffer is reused by the next sub-panel
+}
+
+// Factor panel T (tile column T, every earlier update applied) and publish it: -W1, -W2 in sh.nw, pivot rows in sh.gr.
+// One warp; `guard`: wait (named barrier) until the other warps are done with the previous panel before sh.nw / sh.gr are overwritten.
+__device__ __forceinline__ void gjs_factor(GjsShared& sh, int T, int lane, bool guard, int* __restrict__ info_p, int step) {
+    // rows of this lane (row0, row0 + 32): a quarter warp covers two rows of four different tile rows (conflict-free slab
+    // LDS.128, see the layout note above) and a half warp sixteen different rows mod 16 (conflict-free row-wise STS.64)
+    const int tra = (lane >> 1) & 3;
+    const int row0 = 8 * tra + (lane & 1) + 2 * ((tra >> 1) ^ (lane >> 4)) + 4 * ((lane >> 3) & 1);
+    const int rt = row0 >> 3, ri = row0 & 7, sw = rt & 3;
+    const double2* lo = sh.tiles + (rt * 8 + T) * 32;
+    const double2* hi = lo + 4 * 8 * 32;  // row + 32: four tile rows further
+    double a0[4], a1[4];
     {
-        const int b0 = ((lane >> 3) * 8 + ct) * 32 + (lane & 7) * 4 + 2 * h;
-        const int b1 = b0 + 4 * 8 * 32;  // row + 32: four row tiles further
-        const double2 x0 = sh.tiles[b0], x1 = sh.tiles[b0 + 1], y0 = sh.tiles[b1], y1 = sh.tiles[b1 + 1];
+        const int s0 = (ri * 4) ^ sw, s1 = (ri * 4 + 1) ^ sw;
+        const double2 x0 = lo[s0], x1 = lo[s1], y0 = hi[s0], y1 = hi[s1];
         a0[0] = x0.x; a0[1] = x0.y; a0[2] = x1.x; a0[3] = x1.y;
         a1[0] = y0.x; a1[1] = y0.y; a1[2] = y1.x; a1[3] = y1.y;
     }
-    int gr[4];
-    gjs_step<0>(a0, a1, w0, w1, ps, gr, 4 * pn + 0, lane);
-    gjs_step<1>(a0, a1, w0, w1, ps, gr, 4 * pn + 1, lane);
-    gjs_step<2>(a0, a1, w0, w1, ps, gr, 4 * pn + 2, lane);
-    gjs_step<3>(a0, a1, w0, w1, ps, gr, 4 * pn + 3, lane);
-    double2* pw2 = reinterpret_cast<double2*>(sh.pw[par]);
-    pw2[2 * lane] = make_double2(-w0[0], -w0[1]);
-    pw2[2 * lane + 1] = make_double2(-w0[2], -w0[3]);
-    pw2[2 * (lane + 32)] = make_double2(-w1[0], -w1[1]);
-    pw2[2 * (lane + 32) + 1] = make_double2(-w1[2], -w1[3]);
-    if (lane < 4) sh.gr[par][lane] = lane == 0 ? gr[0] : (lane == 1 ? gr[1] : (lane == 2 ? gr[2] : gr[3]));
-    // right-hand side: rhs <- rhs - W rhs_raw[pivot rows]
-    double s0 = sh.rhs[lane], s1 = sh.rhs[lane + 32];
+    unsigned cand0 = sh.colof[row0] == 0xff ? ~0u : 0u, cand1 = sh.colof[row0 + 32] == 0xff ? ~0u : 0u;
+    double w0[4], w1[4];
+    int g1[4], g2[4];
+    gjs_subpanel(sh, T, 0, a0, a1, w0, w1, g1, cand0, cand1, row0, lane, guard, info_p, step);
+    {
+        // sub-panel 1 <- itself - W1 Xraw[g1, its 4 columns]: the raw rows come from the tiles (nobody writes column T now)
+        const int s2 = (ri * 4 + 2) ^ sw, s3 = (ri * 4 + 3) ^ sw;
+        const double2 x2 = lo[s2], x3 = lo[s3], y2 = hi[s2], y3 = hi[s3];
+        a0[0] = x2.x; a0[1] = x2.y; a0[2] = x3.x; a0[3] = x3.y;
+        a1[0] = y2.x; a1[1] = y2.y; a1[2] = y3.x; a1[3] = y3.y;
+        const double2* tc = sh.tiles + 32 * T;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const double rp = sh.rhs[gr[k]]; s0 = fma(-w0[k], rp, s0); s1 = fma(-w1[k], rp, s1); }
-    __syncwarp();
-    sh.rhs[lane] = s0;
-    sh.rhs[lane + 32] = s1;
+        for (int k = 0; k < 4; ++k) {
+            const int rtk = g1[k] >> 3, rik = (g1[k] & 7) << 2, swk = rtk & 3;
+            const double2 xa = tc[rtk * 256 + ((rik | 2) ^ swk)], xb = tc[rtk * 256 + ((rik | 3) ^ swk)];  // columns 4, 5 and 6, 7
+            a0[0] = fma(-w0[k], xa.x, a0[0]); a0[1] = fma(-w0[k], xa.y, a0[1]); a0[2] = fma(-w0[k], xb.x, a0[2]); a0[3] = fma(-w0[k], xb.y, a0[3]);
+            a1[0] = fma(-w1[k], xa.x, a1[0]); a1[1] = fma(-w1[k], xa.y, a1[1]); a1[2] = fma(-w1[k], xb.x, a1[2]); a1[3] = fma(-w1[k], xb.y, a1[3]);
+        }
+    }
+    gjs_subpanel(sh, T, 1, a0, a1, w0, w1, g2, cand0, cand1, row0, lane, false, info_p, step);
 }
 
-// one warp: tile column ct <- tile column ct - W_p * Xraw[pivot rows of panel p]
-__device__ __forceinline__ void gjs_update_col(GjsShared& sh, const double (&af)[8], int ct, int par, bool own_half, int lane) {
+// B fragments of one tile column for the published panel: Xraw[g1] and X'[g2] = Xraw[g2] - W1[g2, :] Xraw[g1] (4 DFMA).
+// Read before the warp stores any tile of that column.
+struct GjsB {
+    double b1, b2;
+};
+struct GjsRows {  // per lane: offsets of rows g1[0..3], g1[q], g2[q] at its column g8, and the coupling -W1[g2[q], :]
+    double c21[4];
+    int o1[4], o1q, o2;
+};
+__device__ __forceinline__ void gjs_load_rows(const GjsShared& sh, GjsRows& r, int lane) {
     const int g8 = lane >> 2, q = lane & 3;
-    const int r = sh.gr[par][q];
-    const double* tl = reinterpret_cast<const double*>(sh.tiles);
-    double bf = tl[((r >> 3) * 8 + ct) * 64 + ((r & 7) * 4 + (g8 >> 1)) * 2 + (g8 & 1)];
-    if (own_half && g8 < 4) bf = 0.0;  // the panel's own columns are finished
-    double2 c[8];
+    const int g2q = sh.gr[4 + q];
 #pragma unroll
-    for (int rt = 0; rt < 8; ++rt) c[rt] = sh.tiles[(rt * 8 + ct) * 32 + lane];
+    for (int k = 0; k < 4; ++k) { r.o1[k] = gjs_rowoff(sh.gr[k], g8); r.c21[k] = sh.nw[0][k * kGjLdw + g2q]; }
+    r.o1q = gjs_rowoff(sh.gr[q], g8);
+    r.o2 = gjs_rowoff(g2q, g8);
+}
+__device__ __forceinline__ GjsB gjs_load_b(const GjsShared& sh, const GjsRows& r, int ct) {
+    const double* tl = reinterpret_cast<const double*>(sh.tiles) + 64 * ct;
+    double x1[4];
 #pragma unroll
-    for (int rt = 0; rt < 8; ++rt) dmma884(c[rt], af[rt], bf);
+    for (int k = 0; k < 4; ++k) x1[k] = tl[r.o1[k]];
+    GjsB b;
+    b.b1 = tl[r.o1q];
+    b.b2 = tl[r.o2];
 #pragma unroll
-    for (int rt = 0; rt < 8; ++rt) sh.tiles[(rt * 8 + ct) * 32 + lane] = c[rt];
+    for (int k = 0; k < 4; ++k) b.b2 = fma(r.c21[k], x1[k], b.b2);
+    return b;
+}
+// one warp: tile columns ca (and cb) <- themselves - W1 Xraw[g1] - W2 X'[g2] (rank 8: two DMMA per tile).  Four tile rows
+// at a time: their A fragments (-W1, -W2: 16 registers) are loaded once and used for both columns.
+__device__ __forceinline__ void gjs_update_cols(GjsShared& sh, const GjsB& ba, const GjsB& bb, int ca, int cb, bool has_b, int lane) {
+    const int g8 = lane >> 2, q = lane & 3;
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+        double a1[4], a2[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            a1[i] = sh.nw[0][q * kGjLdw + 8 * (4 * hf + i) + g8];
+            a2[i] = sh.nw[1][q * kGjLdw + 8 * (4 * hf + i) + g8];
+        }
+        double2 c[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const int rt = 4 * hf + i; c[i] = sh.tiles[(rt * 8 + ca) * 32 + (lane ^ (rt & 3))]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dmma884(c[i], a1[i], ba.b1);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dmma884(c[i], a2[i], ba.b2);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const int rt = 4 * hf + i; sh.tiles[(rt * 8 + ca) * 32 + (lane ^ (rt & 3))] = c[i]; }
+        if (has_b) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const int rt = 4 * hf + i; c[i] = sh.tiles[(rt * 8 + cb) * 32 + (lane ^ (rt & 3))]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dmma884(c[i], a1[i], bb.b1);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dmma884(c[i], a2[i], bb.b2);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const int rt = 4 * hf + i; sh.tiles[(rt * 8 + cb) * 32 + (lane ^ (rt & 3))] = c[i]; }
+        }
+    }
+}
+
+// right-hand side of row i after the published panel: rhs - W1 rhs[g1] - W2 rhs'[g2], rhs'[g2] = rhs[g2] - W1[g2, :] rhs[g1]
+__device__ __forceinline__ double gjs_rhs_row(const GjsShared& sh, int i) {
+    double r1[4], r2[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { r1[k] = sh.rhs[sh.gr[k]]; r2[k] = sh.rhs[sh.gr[4 + k]]; }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int g = sh.gr[4 + k];
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) r2[k] = fma(sh.nw[0][kk * kGjLdw + g], r1[kk], r2[k]);
+    }
+    double s = sh.rhs[i];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s = fma(sh.nw[0][k * kGjLdw + i], r1[k], s);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s = fma(sh.nw[1][k * kGjLdw + i], r2[k], s);
+    return s;
 }
 
 __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* __restrict__ Kmat, const double* __restrict__ Mmat,
@@ -753,9 +864,11 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
     const double* Ma = ex.Madd ? ex.Madd + p * N * N : nullptr;
 
     // ---- b = M w + f (thread t: row t / 2, every other column pair, partner summed by shuffle) and K into the tiles
-    if (t < 64) sh.pw[0][t] = t < N ? __ldg(Wv + p * pl.Npad + t) : 0.0;  // w staged in the (still unused) W buffer
+    if (t < 64) { sh.nw[0][t] = t < N ? __ldg(Wv + p * pl.Npad + t) : 0.0; sh.colof[t] = 0xff; }  // w staged in the (still unused) W buffer
     const int row = t >> 1, hp = t & 1;
     double s0 = 0.0, s1 = 0.0;
+    // tile idx = w * 16 + i (rt = 2 w + i / 8): slot lane ^ (rt & 3)
+    const int la = lane ^ ((2 * w) & 3), lb = lane ^ ((2 * w + 1) & 3);
     if (Mw) {
         // M w already formed inside the assembly GEMM (N == 64, no dense extras): only K is loaded, two batches in flight
         const double2* ktile = reinterpret_cast<const double2*>(Kp + g8 * 64 + 2 * q);  // + (8 rt) * 64 + 8 ct doubles
@@ -766,9 +879,9 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
         for (int i = 0; i < 8; ++i) { const int idx = w * 16 + 8 + i; b1[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
         if (hp == 0) s0 = __ldg(Mw + p * pl.Npad + row);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + lane] = b0[i];
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + la] = b0[i];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lane] = b1[i];
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lb] = b1[i];
     } else if (N == 64 && !Ma && !Ka) {
         // fast path: four batches of eight 16-byte loads, two batches in flight
         const double2* mrow = reinterpret_cast<const double2*>(Mp + row * 64) + hp;
@@ -779,7 +892,7 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
 #pragma unroll
         for (int i = 0; i < 8; ++i) b1[i] = __ldg(mrow + 2 * (i + 8));
         __syncthreads();  // w visible
-        const double2* w2 = reinterpret_cast<const double2*>(sh.pw[0]) + hp;
+        const double2* w2 = reinterpret_cast<const double2*>(sh.nw[0]) + hp;
 #pragma unroll
         for (int i = 0; i < 8; ++i) { const double2 wv = w2[2 * i]; s0 = fma(b0[i].x, wv.x, s0); s1 = fma(b0[i].y, wv.y, s1); }
 #pragma unroll
@@ -789,22 +902,22 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
 #pragma unroll
         for (int i = 0; i < 8; ++i) { const int idx = w * 16 + 8 + i; b1[i] = __ldg(ktile + (idx >> 3) * 256 + (idx & 7) * 4); }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + lane] = b0[i];
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + i) * 32 + la] = b0[i];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lane] = b1[i];
+        for (int i = 0; i < 8; ++i) sh.tiles[(w * 16 + 8 + i) * 32 + lb] = b1[i];
     } else {
         __syncthreads();
         if (row < N) {
             for (int j = 2 * hp; j < N; j += 4) {
                 const double2 m = gj_load2(Mp, Ma, N, vec, row, j);
-                s0 = fma(m.x, sh.pw[0][j], s0);
-                if (j + 1 < N) s1 = fma(m.y, sh.pw[0][j + 1], s1);
+                s0 = fma(m.x, sh.nw[0][j], s0);
+                if (j + 1 < N) s1 = fma(m.y, sh.nw[0][j + 1], s1);
             }
         }
 #pragma unroll 4
         for (int i = 0; i < 16; ++i) {
             const int idx = w * 16 + i, rt = idx >> 3, ct = idx & 7;
-            sh.tiles[idx * 32 + lane] = gj_load2(Kp, Ka, N, vec, 8 * rt + g8, 8 * ct + 2 * q);
+            sh.tiles[idx * 32 + (lane ^ (rt & 3))] = gj_load2(Kp, Ka, N, vec, 8 * rt + g8, 8 * ct + 2 * q);
         }
     }
     {
@@ -820,42 +933,49 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
     }
     __syncthreads();
 
-    GjsPanelState ps;
-    ps.done0 = ps.done1 = ps.sing = false;
-    ps.rd0 = ps.rd1 = 0.0;
-    ps.pv0 = ps.pv1 = 0;
-    if (w == 0) gjs_factor(sh, ps, 0, lane);
+    const int rot = (int)(blockIdx.x & 3);
+    if (w == rot) gjs_factor(sh, 0, lane, false, info, step);
     __syncthreads();
 #pragma unroll 1
-    for (int pn = 0; pn < 15; ++pn) {
-        const int T = pn >> 1, h = pn & 1, par = pn & 1;
-        const int first = h == 0 ? T : T + 1;  // first live tile column = the one that holds panel pn + 1
-        double af[8];
-#pragma unroll
-        for (int rt = 0; rt < 8; ++rt) af[rt] = sh.pw[par][32 * rt + lane];
-        if (w == 0) {
-            gjs_update_col(sh, af, first, par, h == 0, lane);
+    for (int T = 0; T < 7; ++T) {
+        // panel T is published: its update is pending on tile columns T + 1 .. 7 and on the right-hand side.
+        // role 0: column T + 1, then factors it; roles 1-3: columns T + 1 + role, T + 4 + role (if any); role 1: the right-hand side
+        const int role = (w - (T + 1 + rot)) & 3;
+        const int ca = T + 1 + role, cb = ca + 3;
+        const bool has_a = ca < 8, has_b = role != 0 && cb < 8;
+        GjsB ba, bb;
+        if (has_a) {
+            GjsRows rows;
+            gjs_load_rows(sh, rows, lane);
+            ba = gjs_load_b(sh, rows, ca);
+            bb = ba;
+            if (has_b) bb = gjs_load_b(sh, rows, cb);
+        }
+        if (role == 0) {
+            // the fragments of column T + 1 are read before the named barrier inside gjs_factor; the A fragments too
+            gjs_update_cols(sh, ba, ba, ca, ca, false, lane);
             __syncwarp();
-            gjs_factor(sh, ps, pn + 1, lane);
+            gjs_factor(sh, T + 1, lane, true, info, step);
         } else {
-            for (int ct = first + w; ct < 8; ct += 3) gjs_update_col(sh, af, ct, par, false, lane);
+            double s0 = 0.0, s1 = 0.0;
+            if (role == 1) { s0 = gjs_rhs_row(sh, lane); s1 = gjs_rhs_row(sh, lane + 32); }
+            if (has_a) gjs_update_cols(sh, ba, bb, ca, cb, has_b, lane);
+            // every read of the published panel (sh.nw, sh.gr) is done: the panel warp may overwrite it
+            asm volatile("bar.arrive 1, 128;" ::: "memory");
+            if (role == 1) { __syncwarp(); sh.rhs[lane] = s0; sh.rhs[lane + 32] = s1; }
         }
         __syncthreads();
     }
-    // ---- x_k = rhs[piv_k] / pivot_k, history shuffle, output
-    if (w == 0) {
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-            const int e = lane + 32 * hh;
-            if (e < N) {
-                const double x = hh ? sh.rhs[ps.pv1] * ps.rd1 : sh.rhs[ps.pv0] * ps.rd0;
-                const int64_t s = p * pl.ldu + e;
-                Unm1[s] = Un[s];
-                Un[s] = x;
-                if (uN_out) uN_out[p * out_stride_p + out_off + e] = x;
-            }
+    // ---- x_c = rhs[row] / pivot (rhs after the last panel), c = the column row was the pivot of; history shuffle, output
+    if (t < 64) {
+        const int c = sh.colof[t];
+        if (c < N) {
+            const double x = gjs_rhs_row(sh, t) * reinterpret_cast<const double*>(sh.tiles)[64 * (c >> 3) + gjs_rowoff(t, c & 7)];
+            const int64_t s = p * pl.ldu + c;
+            Unm1[s] = Un[s];
+            Un[s] = x;
+            if (uN_out) uN_out[p * out_stride_p + out_off + c] = x;
         }
-        if (ps.sing) atomicCAS(&info[p], 0, step + 1);
     }
 }
 

@@ -26,20 +26,38 @@ __global__ void k(double* out, long long* cyc, int iters, double a, double b) {
                      r6 = __shfl_sync(0xffffffffu, u + 6, src), r7 = __shfl_sync(0xffffffffu, u + 7, src);
             u = (r0 ^ r1 ^ r2 ^ r3 ^ r4 ^ r5 ^ r6 ^ r7) + threadIdx.x;
         }
+        if (OP == 8) {  // MUFU.RCP64H seed + third-order step (3 dependent DFMA)
+            double x0; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x0) : "d"(x));
+            const double e = fma(-x, x0, 1.0); const double p = fma(e, e, e); x = fma(x0, p, x0) + a;
+        }
+        if (OP == 9) {  // one lane stores 4 doubles, __syncwarp, all lanes read them back (broadcast through shared memory)
+            __shared__ double2 buf[2];
+            if (threadIdx.x == (u & 31)) { buf[0] = make_double2(x, y); buf[1] = make_double2(y, x); }
+            __syncwarp();
+            const double2 p0 = buf[0], p1 = buf[1];
+            __syncwarp();
+            x = p0.x + p1.y * 1e-30; u = u * 5 + 1;
+        }
+        if (OP == 10) {  // dependent LDS.64 chain
+            __shared__ double tab[32];
+            if (i == 0) { tab[threadIdx.x] = (double)((threadIdx.x * 7 + 3) & 31); __syncwarp(); }
+            x = tab[(int)x & 31];
+        }
     }
     long long t1 = clock64();
     if (threadIdx.x == 0) cyc[OP] = t1 - t0;
     if (x + y + u == 123.456) out[0] = x;
 }
 int main() {
-    double* out; long long* cyc; cudaMalloc(&out, 8); cudaMallocManaged(&cyc, 64);
+    double* out; long long* cyc; cudaMalloc(&out, 8); cudaMallocManaged(&cyc, 128);
     const int it = 4096;
     k<0><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<1><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     k<2><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<3><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     k<4><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<5><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     k<6><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<7><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
+    k<8><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<9><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9); k<10><<<1, 32>>>(out, cyc, it, 1.0000001, 1e-9);
     cudaDeviceSynchronize();
-    const char* nm[] = {"dfma", "dmul", "rcp(1/x)", "dmma884", "shfl64", "redux_max+add", "8x redux_or group", "8x shfl32 group"};
-    for (int i = 0; i < 8; ++i) printf("%s: %.1f cycles per dependent op\n", nm[i], (double)cyc[i] / it);
+    const char* nm[] = {"dfma", "dmul", "rcp(1/x)", "dmma884", "shfl64", "redux_max+add", "8x redux_or group", "8x shfl32 group", "fast rcp (+dadd)", "sts->syncwarp->2 lds.128 broadcast", "lds.64 (+cvt)"};
+    for (int i = 0; i < 11; ++i) printf("%s: %.1f cycles per dependent op\n", nm[i], (double)cyc[i] / it);
     return 0;
 }
