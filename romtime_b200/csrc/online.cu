@@ -663,7 +663,8 @@ __device__ __forceinline__ double gjs_rcp(double x) {
 // rb0 / rb1 = 64 | (63 - row): the 7 low key bits (candidate flag, row); cand0 / cand1 = all ones while the row has not been a pivot.
 template <int J>
 __device__ __forceinline__ void gjs_step(GjsShared& sh, double (&a0)[4], double (&a1)[4], double (&w0)[4], double (&w1)[4],
-                                         unsigned& cand0, unsigned& cand1, int (&gr)[4], unsigned rb0, unsigned rb1) {
+                                         unsigned& cand0, unsigned& cand1, int (&gr)[4], double& my_rinv, unsigned rb0, unsigned rb1,
+                                         int lane) {
     // key: high word of |a_J| over the row bits: the pivot is within 2^-13 of the column maximum, the lowest row wins ties
     const unsigned k0 = (((unsigned)__double2hiint(a0[J]) & 0x7fffff80u) | rb0) & cand0;
     const unsigned k1 = (((unsigned)__double2hiint(a1[J]) & 0x7fffff80u) | rb1) & cand1;
@@ -683,6 +684,7 @@ __device__ __forceinline__ void gjs_step(GjsShared& sh, double (&a0)[4], double 
     const double2 ra = sh.rec[J][0], rb = sh.rec[J][1];
     const double r[4] = {ra.x, ra.y, rb.x, rb.y};
     gr[J] = 63 - (int)(mx & 63u);
+    my_rinv = lane == J ? r[J] : my_rinv;  // lane J keeps 1 / pivot of step J for the bookkeeping after the sub-panel
     const double l0 = me0 ? 0.0 : a0[J] * r[J];
     const double l1 = me1 ? 0.0 : a1[J] * r[J];
 #pragma unroll
@@ -703,26 +705,24 @@ __device__ __forceinline__ void gjs_subpanel(GjsShared& sh, int T, int h, double
 #pragma unroll
     for (int j = 0; j < 4; ++j) { w0[j] = 0.0; w1[j] = 0.0; }
     const unsigned rb0 = 64u | (unsigned)(63 - row0), rb1 = 64u | (unsigned)(31 - row0);
-    gjs_step<0>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
-    gjs_step<1>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
-    gjs_step<2>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
-    gjs_step<3>(sh, a0, a1, w0, w1, cand0, cand1, gr, rb0, rb1);
+    double rv = 0.0;
+    gjs_step<0>(sh, a0, a1, w0, w1, cand0, cand1, gr, rv, rb0, rb1, lane);
+    gjs_step<1>(sh, a0, a1, w0, w1, cand0, cand1, gr, rv, rb0, rb1, lane);
+    gjs_step<2>(sh, a0, a1, w0, w1, cand0, cand1, gr, rv, rb0, rb1, lane);
+    gjs_step<3>(sh, a0, a1, w0, w1, cand0, cand1, gr, rv, rb0, rb1, lane);
     // the other warps have read what they need of the previous panel: sh.nw / sh.gr may be overwritten
     if (guard) asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll
     for (int k = 0; k < 4; ++k) { sh.nw[h][k * kGjLdw + row0] = -w0[k]; sh.nw[h][k * kGjLdw + row0 + 32] = -w1[k]; }
     if (lane < 4) {
-        // lane J records pivot J.  1 / pivot is entry J of step J's record, still in the record buffer; it is parked in the
-        // pivot entry (g, col) -- the column is finished, nobody reads it again as a matrix entry --, the column in colof[g];
-        // a vanished pivot (1 / pivot not finite) flags the parameter
+        // lane J records pivot J: 1 / pivot is parked in the pivot entry (g, col) -- the column is finished, nobody reads it
+        // again as a matrix entry --, the column in colof[g]; a vanished pivot (1 / pivot not finite) flags the parameter
         const int g = lane == 0 ? gr[0] : (lane == 1 ? gr[1] : (lane == 2 ? gr[2] : gr[3]));
-        const double rv = reinterpret_cast<const double*>(sh.rec)[5 * lane];
         sh.gr[4 * h + lane] = g;
         reinterpret_cast<double*>(sh.tiles)[64 * T + gjs_rowoff(g, 4 * h + lane)] = rv;
         sh.colof[g] = (unsigned char)(8 * T + 4 * h + lane);
         if (!(fabs(rv) < 1.7976931348623157e308)) atomicCAS(info_p + blockIdx.x, 0, step + 1);
     }
-    __syncwarp();  // the record buffer is reused by the next sub-panel
 }
 
 // Factor panel T (tile column T, every earlier update applied) and publish it: -W1, -W2 in sh.nw, pivot rows in sh.gr.
