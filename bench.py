@@ -6,9 +6,10 @@
 Workload (BASELINE.json configs[4] + configs[2]):
   * online: batched ROM sweep, B = 65,536 parameters (sharded over the ranks: strong scaling),
     reduced dimension N = 64, five MDEIM operators + one DEIM vector with m = 128 collateral modes,
-    BDF2.  One bench "step" = the whole batch advanced by --nt-per-step implicit time steps
-    (default 100; the 1000-step sweep of the config is ten such steps, cost per time step is constant).
-    metric = ROM param*timesteps/s.
+    BDF2.  One bench "step" = ONE uninterrupted sweep of the whole batch over --nt-per-step implicit time steps from the
+    zero initial condition (default 1000 = the named config: 33.5 GB of history per step, written to HBM).
+    metric = ROM param*timesteps/s.  The line also carries a 1000-step parity figure against the CPU reference, an
+    m = 16 sweep, the POD in both storage orders and the C4 / certification legs.
   * pod (reported in the same line): orth of a synthetic 1,000,000 x 4096 fp64 snapshot matrix, num=64.
 """
 import argparse
@@ -23,6 +24,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "rom_param_timesteps_per_s"
+# dominant kernel's DRAM traffic per launch from the committed ncu capture of this round (K written once, M never stored)
+NCU_GEMM_PROFILE = "profiles/r2_sweep_ncu.md"
+NCU_GEMM_DRAM_BYTES_PER_14208 = 532.1e6
 UNIT = "param*timesteps/s"
 
 
@@ -33,7 +37,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--params", type=int, default=65536)
-    ap.add_argument("--nt-per-step", type=int, default=100)
+    ap.add_argument("--nt-per-step", type=int, default=1000)
+    ap.add_argument("--e2e-steps", type=int, default=3, help="timed repetitions of the host-to-host leg (at most --steps)")
     ap.add_argument("--m", type=int, default=128)
     ap.add_argument("--pod-rows", type=int, default=1_000_000)
     ap.add_argument("--pod-cols", type=int, default=4096)
@@ -51,13 +56,16 @@ def workload_config(a, world):
         "bdf": 2, "dt": 1e-3, "timesteps_per_bench_step": a.nt_per_step,
         "sharding": f"parameters over {world} GPU(s), no collective",
         "l2": "working set per time step (K buffer 466 MB per 14,208-parameter chunk, written by the GEMM and read by the solve) exceeds the 126 MB L2; no explicit flush",
+        "history": "B x nt x N written to HBM every step (33.5 GB per 1000-step sweep at B = 65,536)",
     }
 
 
 # ------------------------------------------------------------------------------- reference arm
 def reference_arm(a, out_fd):
-    """CPU arm: the oracle port of RomConstructorNonlinear.solve (the reference itself needs FEniCS and
-    cannot run here) on all host cores; each step = `cores` parameters x a bounded number of time steps."""
+    """CPU arm: the UNMODIFIED reference's RomConstructorNonlinear.solve (rom/rom.py:430-555, stock GMRES) from the
+    vendored copy oracle/_ref, one process per host core (oracle/cpu_bench.py); the oracle port only if no reference
+    tree travelled.  Each bench step = `cores` parameters x a bounded number of time steps of the same C5 model; the
+    worker pool is created and warmed before the timer starts."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -66,21 +74,24 @@ def reference_arm(a, out_fd):
 
     cores = os.cpu_count() or 1
     nt = 300  # bounded sample per bench step: a few seconds on every core
-    for _ in range(max(a.warmup, 0) and 1):
-        cpu_bench.online_sweep_rate(cores, 64, a.m, 2)
-    t0 = time.perf_counter()
-    units = 0
-    for _ in range(a.steps):
-        rate, wall, _ = cpu_bench.online_sweep_rate(cores, 64, a.m, nt)
-        units += cores * nt
-    total = time.perf_counter() - t0
-    value = units / total
-    sample = f"{cores} parameters x {nt} BDF2 steps per bench step, one worker process per core, BLAS threads 1"
+    pool = cpu_bench.SweepPool(cores, 64, a.m)
+    try:
+        for _ in range(min(a.warmup, 1)):
+            pool.run(20)
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            pool.run(nt)
+        total = time.perf_counter() - t0
+        direct_rate = pool.run(nt, solver="direct")[0] if pool.kind == "reference" else None
+    finally:
+        pool.close()
+    value = cores * nt * a.steps / total
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": total / a.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a, a.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": pool.kind, "sample": pool.describe(nt),
+                         "value_with_direct_solve_hook": direct_rate},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -175,7 +186,7 @@ def pod_leg(a, torch, kernels, world, rank):
         e[1].record()
         w, W, sweeps = kernels.sym_eig(G)
         e[2].record()
-        Q, s, energy, VT, _ = podmod.orth_device(S, num=64)
+        Q, s, energy, VT, info = podmod.orth_device(S, num=64)
         e[3].record()
         torch.cuda.synchronize()
         t_gram, t_eig, t_orth = e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2]), e[2].elapsed_time(e[3])
@@ -185,35 +196,71 @@ def pod_leg(a, torch, kernels, world, rank):
     peak = kernels.fp64_peak_tflops()
     flops = float(Nh) * n * (n + 1)
     QtQ = (Q.t() @ Q - torch.eye(Q.shape[1], dtype=torch.float64, device=dev)).abs().max().item()
+    rest = max(t_orth - t_gram - t_eig, 0.0)
     res = {
-        "shape": [Nh, n], "num": 64, "svd_time_ms": t_orth, "gram_ms": t_gram, "eig_ms": t_eig,
-        "lift_and_rest_ms": max(t_orth - t_gram - t_eig, 0.0), "gram_tflops_sym_half": flops / t_gram * 1e-9,
+        "shape": [Nh, n], "num": 64, "order": "C (np.hstack, rom/rom.py:368)", "svd_time_ms": t_orth, "gram_ms": t_gram, "eig_ms": t_eig,
+        "lift_refinement_and_rest_ms": rest, "lift_refinement_share_of_orth": rest / t_orth,
+        "gram_tflops_sym_half": flops / t_gram * 1e-9,
         "gram_frac_of_fp64_peak": flops / t_gram * 1e-9 / peak, "S_GBps_whole_orth": 8.0 * Nh * n / t_orth * 1e-6,
         "eig_sweeps": sweeps, "QtQ_minus_I_max": QtQ, "energy_last": float(energy[-1]),
+        "refinement": {k: info[k] for k in ("levels", "rank_gram", "candidates", "passes", "defect") if k in info},
         "singular_values_head": [float(x) for x in s[:4]],
     }
-    del S, G, W, Q
+    del G, W, Q
+    try:
+        # the same matrix stored column-major (np.array(list).T, deim/deim.py:384): the Gram kernel reads it through the MN-major tensor map
+        Sf = torch.empty((n, Nh), dtype=torch.float64, device=dev)
+        for r0 in range(0, Nh, rows):
+            Sf[:, r0:min(Nh, r0 + rows)] = S[r0:min(Nh, r0 + rows)].t()
+        del S
+        Sf = Sf.t()
+        tf = None
+        for it in range(2):
+            e0, e1 = ev(), ev()
+            e0.record()
+            Qf, sf, _, _, _ = podmod.orth_device(Sf, num=64)
+            e1.record()
+            torch.cuda.synchronize()
+            tf = e0.elapsed_time(e1) if tf is None else min(tf, e0.elapsed_time(e1))
+        res["svd_time_ms_F_order"] = tf
+        res["F_order_singular_values_max_rel_vs_C_order"] = float(abs(sf[:64] - s[:64]).max() / s[0])
+        del Sf, Qf
+    except Exception as exc:  # report, never hide
+        res["svd_time_ms_F_order"] = repr(exc)
     torch.cuda.empty_cache()
     if rank == 0 and not a.skip_cpu:
-        # CPU baseline: the oracle's orth (rom/pod.py:7-62: column norms + LAPACK gesvd, all BLAS threads) on
-        # a bounded sample of the same family; the full-size figure is an O(Nh n^2) EXTRAPOLATION and is labelled as one
+        # CPU baseline (SURVEY.md 8d / BASELINE.md 3): the oracle's orth (rom/pod.py:7-62: column norms + LAPACK gesvd, all BLAS
+        # threads) on 1,000,000 x 512 of the same family; the full-size figure is an O(Nh n^2) EXTRAPOLATION (x 64) and labelled so
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import numpy as np
         import romtime_oracle as orc_mod
         from romtime_b200 import synthetic
 
-        nh_s, n_s = 16000, 1024
-        Ss = synthetic.pod_snapshots(nh_s, n_s, seed=1003)
+        nh_s, n_s = min(Nh, 1_000_000), min(n, 512)
+        Ss = np.empty((nh_s, n_s))
+        for r0 in range(0, nh_s, 100_000):  # generated in row slabs: the closed form needs a rows x modes temporary
+            r1 = min(nh_s, r0 + 100_000)
+            Ss[r0:r1] = synthetic.pod_snapshots(nh_s, n_s, seed=1003, row0=r0, rows=r1 - r0)
         t0 = time.perf_counter()
         Qc, sc, _ = orc_mod.orth(Ss, num=64)
         wall = time.perf_counter() - t0
         res["cpu_orth_sample_ms"] = wall * 1e3
         res["cpu_orth_sample"] = f"oracle orth (scipy gesvd) on {nh_s} x {n_s}, {os.cpu_count()} host cores, BLAS default threads"
         res["cpu_orth_extrapolated_full_ms"] = wall * 1e3 * (Nh / nh_s) * (n / n_s) ** 2
-        res["cpu_orth_note"] = "extrapolated by Nh n^2 from the sample, not measured at full size"
-        # the device path on the same sample, for a like-for-like parity figure
-        Qd, sd, _, _, _ = podmod.orth_device(Ss, num=64)
+        res["cpu_orth_note"] = f"full size extrapolated by Nh n^2 (x {(Nh / nh_s) * (n / n_s) ** 2:.0f}) from the sample, not measured"
+        # the device path on the same sample, for a like-for-like time and parity figure
+        Sd = kernels.to_device(Ss)
+        podmod.orth_device(Sd, num=64)
+        e0, e1 = ev(), ev()
+        e0.record()
+        Qd, sd, _, _, _ = podmod.orth_device(Sd, num=64)
+        e1.record()
+        torch.cuda.synchronize()
+        res["gpu_orth_same_sample_ms"] = e0.elapsed_time(e1)
         res["sample_singular_values_max_rel"] = float(np.abs(sd[:64] - sc[:64]).max() / sc[0])
+        dots = np.abs(np.sum(Qd.cpu().numpy() * Qc, axis=0))
+        res["sample_modes_max_abs_1_minus_dot"] = float(np.abs(dots - 1.0).max())
+        del Sd, Qd
     return res
 
 
@@ -250,12 +297,14 @@ def c4_leg(a, torch, kernels, with_cpu):
     blk = 8.0 * nnz * m * (m / 8 + 1) / 2       # what the 8-column blocked kernel streams from HBM
     hbm = hbm_peak_gbs()
     res = {"shape": [nnz, n], "m": m, "pod_ms": t_pod, "pod_GBps_of_S": 8.0 * nnz * n / t_pod * 1e-6,
-           "sigma_m_over_sigma_1": float(s[m - 1] / s[0]), "greedy_ms": t_gr,
-           "greedy_algorithmic_GBps": alg / t_gr * 1e-6, "greedy_algorithmic_frac_of_hbm_peak": alg / t_gr * 1e-6 / hbm,
-           "greedy_blocked_traffic_GBps": blk / t_gr * 1e-6, "greedy_us_per_point": 1e3 * t_gr / m,
-           "hbm_peak_GBps": hbm, "unique_dofs": int(torch.unique(dofs).numel()),
-           "bound": "hbm by SURVEY.md 8d's algorithmic bytes (8 Nh m (m+1) / 2 = 13.2 GB -> 2.0 ms at peak); the blocked kernel "
-                    "streams 8x less and is bound by its m grid-wide arg-max exchanges"}
+           "sigma_m_over_sigma_1": float(s[m - 1] / s[0]), "QtQ_minus_I_max": float((Q.t() @ Q - torch.eye(m, dtype=torch.float64, device=Q.device)).abs().max().item()),
+           "greedy_ms": t_gr,
+           "greedy_traffic_GBps": blk / t_gr * 1e-6, "greedy_frac_of_hbm_peak": blk / t_gr * 1e-6 / hbm,
+           "greedy_traffic_model": "bytes the 8-column blocked kernel streams: 8 Nh m (m / 8 + 1) / 2 = 1.74 GB (ncu dram__bytes_read 1.28 GB, the rest L2 hits)",
+           "greedy_us_per_point": 1e3 * t_gr / m, "hbm_peak_GBps": hbm, "unique_dofs": int(torch.unique(dofs).numel()),
+           "survey_8d_unblocked_bytes_GBps": alg / t_gr * 1e-6,
+           "bound": "latency: m grid-wide arg-max exchanges at ~10 us each; HBM at 0.2 of peak.  SURVEY.md 8d's unblocked byte model "
+                    "(8 Nh m (m+1) / 2 = 13.2 GB -> 2.0 ms at the HBM peak) is kept as context only: the blocked kernel streams 8x less"}
     if with_cpu:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import romtime_oracle as orc_mod
@@ -291,17 +340,27 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
-    cpu_baseline = None
+    cpu_baseline, cpu_traj, cpu_traj_gmres = None, None, None
     if rank == 0 and world == 1 and not a.skip_cpu:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import cpu_bench
 
         cores = os.cpu_count() or 1
         nt_cpu = 1000  # one full C5 trajectory per core: 10-20 s of CPU work
-        rate, wall, _ = cpu_bench.online_sweep_rate(cores, 64, a.m, nt_cpu)
-        cpu_baseline = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"oracle rom_sweep (NumPy port of rom/rom.py:430-555): {cores} parameters x {nt_cpu} "
-                                  f"BDF2 steps, one process per core, BLAS threads 1, {wall:.1f} s"}
+        pool = cpu_bench.SweepPool(cores, 64, a.m)
+        try:
+            rate, wall, cpu_traj_gmres = pool.run(nt_cpu, keep=True)
+            cpu_baseline = {"value": rate, "unit": UNIT, "cores": cores, "kind": pool.kind,
+                            "sample": pool.describe(nt_cpu) + f", {wall:.1f} s"}
+            if pool.kind == "reference":
+                # the same trajectories with the reference's algebraic-solver hook swapped for a direct solve: what the
+                # device path (dense pivoted solve) is compared with at 1e-10; stock GMRES carries its own 1e-10 stopping error
+                rate_d, wall_d, cpu_traj = pool.run(nt_cpu, keep=True, solver="direct")
+                cpu_baseline["value_with_direct_solve_hook"] = rate_d
+            else:
+                cpu_traj, cpu_traj_gmres = cpu_traj_gmres, None
+        finally:
+            pool.close()
 
     import torch
     import torch.distributed as dist
@@ -317,7 +376,8 @@ def main():
     lo, hi = rank * B // world, (rank + 1) * B // world
     model = synthetic.make_piston_model(N=N, m=m, seed=1005)
     dm = kernels.DeviceRomModel(model)
-    mus_host = torch.from_numpy(synthetic.sample_mus(B, seed=1005)[lo:hi].copy()).pin_memory()
+    mus_all = synthetic.sample_mus(B, seed=1005)
+    mus_host = torch.from_numpy(mus_all[lo:hi].copy()).pin_memory()
     mus = mus_host.to(dev)
     Bl = hi - lo
 
@@ -326,11 +386,32 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- 1000-step parity against the CPU reference on the parameters its workers ran (the first `cores` of the batch)
+    parity = None
+    if cpu_traj is not None:
+        import numpy as np
+
+        nb = len(cpu_traj)
+        up, ip = kernels.online_sweep(dm, mus_all[:nb], 1000, dt, bdf=2)
+        up = up.cpu().numpy().transpose(0, 2, 1)  # (nb, N, nt) like RomSolutionsStorage.rom
+        rel = lambda x, y: float(np.max(np.abs(x - y)) / np.max(np.abs(y)))  # noqa: E731
+        parity = {"parameters": nb, "steps": 1000, "parity_1000_steps_max_rel": max(rel(up[i], cpu_traj[i]) for i in range(nb)),
+                  "against": "reference RomConstructorNonlinear.solve with the algebraic-solver hook = np.linalg.solve"
+                             if cpu_traj_gmres is not None else "oracle rom_sweep (NumPy port, direct solve)",
+                  "last_step_max_rel": max(rel(up[i][:, -1], cpu_traj[i][:, -1]) for i in range(nb)),
+                  "singular_solves": int(ip.ne(0).sum().item())}
+        if cpu_traj_gmres is not None:
+            parity["vs_stock_gmres_max_rel"] = max(rel(up[i], cpu_traj_gmres[i]) for i in range(nb))
+            parity["reference_direct_vs_reference_gmres_max_rel"] = max(rel(cpu_traj[i], cpu_traj_gmres[i]) for i in range(nb))
+        del up
+
+    out = torch.empty((Bl, nt, N), dtype=torch.float64, device=dev)
+
     def step_resident():
-        return kernels.online_sweep(dm, mus, nt, dt, bdf=2, history=True)
+        return kernels.online_sweep(dm, mus, nt, dt, bdf=2, history=True, out=out)
 
     for _ in range(a.warmup):
-        out, info = step_resident()
+        _, info = step_resident()
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -342,7 +423,7 @@ def main():
     barrier()
     e0.record()
     for _ in range(a.steps):
-        out, info = step_resident()
+        _, info = step_resident()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -358,24 +439,65 @@ def main():
     value = float(B) * nt * a.steps / (ms * 1e-3)
 
     # ---- end to end: host mus -> device, sweep, history back to pinned host memory ----
-    hist_host = torch.empty((Bl, nt, N), dtype=torch.float64).pin_memory()
+    # public host-to-host call (= RomConstructor*.solve_batch(..., to_host=True)): mus from pinned host memory, the history
+    # lands in pinned host memory; the sweep runs in 100-step segments and every finished time slab is copied out while the
+    # next segment is computed (rt_online_sweep_segment_f64 + rt_memcpy2d_async)
+    e2e_steps = max(1, min(a.steps, a.e2e_steps))
+    cert_rows = min(Bl, 8192)
+    cert_u = out[:cert_rows].clone()  # kept for the certification leg
+    del out
+    torch.cuda.empty_cache()
+    hist_host = torch.empty((Bl, nt, N), dtype=torch.float64, pin_memory=True)
 
     def step_e2e():
-        # public host-to-host call: mus from pinned host memory, the history lands in pinned host memory (the
-        # device-to-host copy of a chunk overlaps the next chunk's sweep)
         kernels.online_sweep_to_host(dm, mus_host, nt, dt, bdf=2, out_host=hist_host)
         torch.cuda.synchronize()
 
     step_e2e()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(a.steps):
+    for _ in range(e2e_steps):
         step_e2e()
     barrier()
     te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = float(B) * nt * a.steps / float(te.item())
+    e2e_value = float(B) * nt * e2e_steps / float(te.item())
+    e2e_matches = bool(torch.equal(hist_host[:cert_rows], cert_u.cpu()))
+    del hist_host
+
+    # ---- the same sweep with m = 16 collateral modes per operator (SURVEY.md 8d names m in {16, 128}): the solve, not the
+    # assembly GEMM, dominates there
+    m16 = None
+    try:
+        model16 = synthetic.make_piston_model(N=N, m=16, seed=1005)
+        dm16 = kernels.DeviceRomModel(model16)
+        nt16 = min(nt, 100)
+        out16 = torch.empty((Bl, nt16, N), dtype=torch.float64, device=dev)
+        for _ in range(2):
+            kernels.online_sweep(dm16, mus, nt16, dt, bdf=2, out=out16)
+        kernels.profile_enable(True)
+        kernels.profile_read()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(3):
+            _, info16 = kernels.online_sweep(dm16, mus, nt16, dt, bdf=2, out=out16)
+        f1.record()
+        barrier()
+        prof16 = kernels.profile_read()
+        kernels.profile_enable(False)
+        t16 = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t16, op=dist.ReduceOp.MAX)
+        tot16 = sum(v[0] for v in prof16.values())
+        m16 = {"value": float(B) * nt16 * 3 / (float(t16.item()) * 1e-3), "unit": UNIT, "collateral_modes": 16, "timesteps": nt16,
+               "steps": 3, "kernel_shares": {k: v[0] / tot16 for k, v in prof16.items()},
+               "kernel_us_per_launch": {k: 1e3 * v[0] / v[1] for k, v in prof16.items()},
+               "singular_solves": int(info16.ne(0).sum().item())}
+        del out16, dm16
+    except Exception as exc:  # report, never hide
+        m16 = {"error": repr(exc)}
 
     # ---- roofline of the dominant kernel (assembly GEMM on the FP64 DMMA pipe) ----
     peak = kernels.fp64_peak_tflops()
@@ -391,8 +513,9 @@ def main():
                 "unit": "TFLOP/s", "frac": ach / peak,
                 "peak_source": "FP64 DMMA peak measured in this run (rt_fp64_peak_tflops; MEASURED_PEAKS.json has no fp64 entry)",
                 "avg_launch_ms": g_ms / g_n, "launches_timed": g_n, "share_of_step": g_ms / total_prof,
-                "traffic": 532.1e6 * chunk / 14208.0,
-                "traffic_source": "dram bytes read+write per launch (532.1 MB at a 14208-parameter chunk, scaled to this chunk: K written once, M never stored), ncu --set full, profiles/r1i_sweep_ncu.md",
+                "traffic": NCU_GEMM_DRAM_BYTES_PER_14208 * chunk / 14208.0,
+                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the ncu --set full capture of the same "
+                                  "sweep at one 14,208-parameter chunk (" + NCU_GEMM_PROFILE + "), scaled to this chunk; ncu cannot run inside the timed region",
                 "kernel_shares": {k: v[0] / total_prof for k, v in prof.items()}}
 
     # ---- certification leg: S-ROM estimator over every (parameter, step) of the last sweep
@@ -400,6 +523,7 @@ def main():
     try:
         g = torch.Generator(device=dev).manual_seed(1006)
         Vs = torch.linalg.qr(torch.randn((20000, N), dtype=torch.float64, device=dev, generator=g))[0]
+        out = cert_u  # the first parameters of the last timed sweep (the full 33.5 GB history has been released)
         srom = out + 1e-3 * torch.randn(out.shape, dtype=torch.float64, device=dev, generator=g)
         G, _ = kernels.pod_gram(Vs, normalize=False)
         kernels.rom_difference(out, srom, Vs)
@@ -412,7 +536,7 @@ def main():
         c2.record()
         torch.cuda.synchronize()
         t_est, t_sum = c0.elapsed_time(c1), c1.elapsed_time(c2)
-        rows = float(Bl) * nt
+        rows = float(out.shape[0]) * nt
         cert = {"rows": int(rows), "estimator_ms": t_est, "summary_ms": t_sum,
                 "estimator_GBps": 8.0 * rows * (2 * N + 1) / t_est * 1e-6,
                 "estimator_frac_of_hbm_peak": 8.0 * rows * (2 * N + 1) / t_est * 1e-6 / hbm_peak_gbs(),
@@ -423,16 +547,17 @@ def main():
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import romtime_oracle as orc_mod
 
-            nb = 64
-            hu, hs, hv = out[:nb].cpu().numpy(), srom[:nb].cpu().numpy(), Vs.cpu().numpy()
+            nb, ns = 64, min(nt, 100)
+            hu, hs, hv = out[:nb, :ns].cpu().numpy(), srom[:nb, :ns].cpu().numpy(), Vs.cpu().numpy()
             t0 = time.perf_counter()
             ref = orc_mod.rom_difference_batch(hu, hs, hv)
             wall = time.perf_counter() - t0
-            cert["cpu_rows_per_s"] = nb * nt / wall
-            cert["cpu_sample"] = f"oracle rom_difference_batch (utils.py:173-212 per row), {nb} parameters x {nt} steps, 1 core, {wall:.1f} s"
+            cert["cpu_rows_per_s"] = nb * ns / wall
+            cert["cpu_sample"] = f"oracle rom_difference_batch (utils.py:173-212 per row), {nb} parameters x {ns} steps, 1 core, {wall:.1f} s"
             cert["gpu_rows_per_s"] = rows / (t_est * 1e-3)
-            cert["parity_max_rel"] = float(abs(err[:nb].cpu().numpy() - ref).max() / abs(ref).max())
-        del srom, err, summ, Vs
+            cert["parity_max_rel"] = float(abs(err[:nb, :ns].cpu().numpy() - ref).max() / abs(ref).max())
+        del srom, err, summ, Vs, out, cert_u
+        torch.cuda.empty_cache()
     except Exception as exc:  # report, never hide
         cert = {"error": repr(exc)}
 
@@ -456,8 +581,12 @@ def main():
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": workload_config(a, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Bl * 3 * 8) * world,
-                    "d2h_bytes_per_step": int(Bl * nt * N * 8) * world},
+                    "d2h_bytes_per_step": int(Bl * nt * N * 8) * world, "steps": e2e_steps,
+                    "api": "kernels.online_sweep_to_host = RomConstructor*.solve_batch(..., to_host=True): 100-step segments, every "
+                           "finished time slab copied to pinned host memory while the next segment runs",
+                    "host_history_equals_device_history": e2e_matches},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_baseline,
+            "parity_1000_steps": parity, "sweep_m16": m16,
             "pod": pod, "mdeim_c4": c4, "certification": cert, "singular_solves": bad,
         }
         emit(line, out_fd)

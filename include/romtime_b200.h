@@ -200,6 +200,20 @@ int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const doub
                              int64_t nt, double dt, int bdf, double* uN_last, int* info,
                              void* stream);
 
+/* Steps n0 .. n1 - 1 of the same nt-step sweep, with the state carried by the caller (Un, Unm1: B x N row-major, device;
+ * zeroed by the call when n0 == 0, updated in place).  Consecutive segments [0, n1), [n1, n2), ... reproduce the
+ * uninterrupted sweep bit for bit (same time accumulation t += dt, rom/rom.py:476-479; same BDF start-up, :481-483).
+ * Every segment writes its rows [b][n0 .. n1 - 1][:] of uN_out (B x nt x N): the host-delivered sweep copies a finished
+ * time slab to pinned memory (rt_memcpy2d_async) while the next segment is computed. */
+int rt_online_sweep_segment_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B,
+                                int64_t nt, int64_t n0, int64_t n1, double dt, int bdf, double* Un,
+                                double* Unm1, double* uN_out, int* info, void* stream);
+
+/* cudaMemcpy2DAsync on `stream`: `rows` rows of `width_bytes`, pitches in bytes; to_host != 0: device -> host,
+ * else host -> device.  (RomSolutionsStorage histories leave the device through this call, base.py:70-79.) */
+int rt_memcpy2d_async(rt_handle* h, void* dst, int64_t dst_pitch, const void* src, int64_t src_pitch,
+                      int64_t width_bytes, int64_t rows, int to_host, void* stream);
+
 /* ONE implicit step for a batch of B parameters with caller-supplied sampled entries -- the form the
  * reference's own time loop needs when the assemble(mu, t, entries[, u_n]) callback stays on the host
  * (FEniCS; rom/rom.py:486-492 with deim/deim.py:437-445 inside every assemble_* call):

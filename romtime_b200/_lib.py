@@ -66,6 +66,9 @@ SIGNATURES = {
     "rt_assemble_batch_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp]),
     "rt_online_sweep_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_i64, c_dbl, c_int, c_vp, c_vp, c_vp]),
     "rt_online_sweep_last_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_i64, c_dbl, c_int, c_vp, c_vp, c_vp]),
+    "rt_online_sweep_segment_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_i64, c_i64, c_i64, c_dbl, c_int, c_vp, c_vp,
+                                            c_vp, c_vp, c_vp]),
+    "rt_memcpy2d_async": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_int, c_vp]),
     "rt_online_step_f64": (c_int, [c_vp, ctypes.POINTER(RomModel), c_vp, c_i64, c_dbl, c_int, c_i64, c_vp, c_vp, c_vp, c_vp,
                                    c_vp, c_vp, c_vp]),
     "rt_rom_difference_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp]),

@@ -41,6 +41,18 @@ extern "C" const char* rt_last_error(const rt_handle* h) { return h ? h->err : "
 
 extern "C" int64_t rt_launch_count(const rt_handle* h) { return h ? h->launches : 0; }
 
+// Strided device-to-host / host-to-device copy on a stream (cudaMemcpy2DAsync): a time slab [:, n0:n1, :] of the sweep
+// history (B x nt x N) goes to pinned host memory as ONE copy while later steps are computed.
+extern "C" int rt_memcpy2d_async(rt_handle* h, void* dst, int64_t dst_pitch, const void* src, int64_t src_pitch, int64_t width_bytes,
+                                 int64_t rows, int to_host, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, dst && src && width_bytes >= 1 && rows >= 1 && dst_pitch >= width_bytes && src_pitch >= width_bytes);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    RT_CUDA(h, cudaMemcpy2DAsync(dst, (size_t)dst_pitch, src, (size_t)src_pitch, (size_t)width_bytes, (size_t)rows,
+                                 to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice, rt_stream(stream)));
+    return RT_OK;
+}
+
 // Register-resident DMMA loop: 8 independent m8n8k4 accumulators per warp (see tools/fp64_peak.cu).
 __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters, double a, double b) {
     double c0[8], c1[8];

@@ -1408,25 +1408,42 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     return rc;
 }
 
-int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, double dt, int bdf,
-               double* uN_out, double* uN_last, int* info, cudaStream_t st) {
-    RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1);
+// Steps n0 .. n1 - 1 of the nt-step sweep.  Un_state / Unm1_state == nullptr: the whole sweep from the zero initial condition
+// with the state in the handle's scratch (n0 must be 0); otherwise the caller-owned state (B x N row-major, updated in
+// place) carries the sweep from one segment to the next.
+int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt, int64_t n0, int64_t n1, double dt,
+               int bdf, double* Un_state, double* Unm1_state, double* uN_out, double* uN_last, int* info, cudaStream_t st) {
+    RT_REQUIRE(h, model && mu && info && B >= 1 && nt >= 1 && n0 >= 0 && n0 < n1 && n1 <= nt);
     RT_REQUIRE(h, bdf == 1 || bdf == 2);
+    RT_REQUIRE(h, (Un_state != nullptr) == (Unm1_state != nullptr));
+    RT_REQUIRE(h, Un_state || n0 == 0);
     SweepCtx cx;
     int rc = sweep_setup(h, model, B, true, st, cx);
     if (rc) return rc;
     SweepPlan& pl = cx.pl;
     SweepBuffers& b = cx.b;
-    RT_CUDA(h, cudaMemsetAsync(info, 0, (size_t)B * sizeof(int), st));
+    if (n0 == 0) RT_CUDA(h, cudaMemsetAsync(info, 0, (size_t)B * sizeof(int), st));
+    if (Un_state) pl.ldu = pl.N;
     const LuExtras none{nullptr, nullptr, nullptr};
+    double t0 = 0.0;
+    for (int64_t n = 0; n < n0; ++n) t0 += dt;  // the same accumulation as the uninterrupted loop (rom.py:476-479)
     for (int64_t p0 = 0; p0 < B; p0 += cx.chunk) {
         pl.Bc = (int)((B - p0) < cx.chunk ? (B - p0) : cx.chunk);
-        const size_t state_bytes = (size_t)pl.Bcpad * pl.Npad * sizeof(double);
-        RT_CUDA(h, cudaMemsetAsync(b.Un, 0, state_bytes, st));    // zero initial condition (rom.py:451-452)
-        RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, state_bytes, st));  // uN_n1 = zeros, not None (rom.py:456-460)
+        if (Un_state) {
+            b.Un = Un_state + p0 * pl.N;
+            b.Unm1 = Unm1_state + p0 * pl.N;
+            if (n0 == 0) {
+                RT_CUDA(h, cudaMemsetAsync(b.Un, 0, (size_t)pl.Bc * pl.N * sizeof(double), st));
+                RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, (size_t)pl.Bc * pl.N * sizeof(double), st));
+            }
+        } else {
+            const size_t state_bytes = (size_t)pl.Bcpad * pl.Npad * sizeof(double);
+            RT_CUDA(h, cudaMemsetAsync(b.Un, 0, state_bytes, st));    // zero initial condition (rom.py:451-452)
+            RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, state_bytes, st));  // uN_n1 = zeros, not None (rom.py:456-460)
+        }
         const double* mu_c = mu + p0 * 3;
-        double t = 0.0;
-        for (int64_t n = 0; n < nt; ++n) {
+        double t = t0;
+        for (int64_t n = n0; n < n1; ++n) {
             t += dt;  // same accumulation as the reference loop (rom.py:476-479)
             StepOut o{nullptr, 0, 0, info + p0, (int)n};
             if (uN_out) { o.uN_out = uN_out + p0 * nt * pl.N; o.stride_p = nt * pl.N; o.off = n * pl.N; }
@@ -1445,7 +1462,16 @@ extern "C" int rt_online_sweep_f64(rt_handle* h, const rt_rom_model* model, cons
     if (!h) return RT_EINVAL;
     RT_REQUIRE(h, uN_out);
     RT_CUDA(h, cudaSetDevice(h->device));
-    return sweep_impl(h, model, mu, B, nt, dt, bdf, uN_out, nullptr, info, rt_stream(stream));
+    return sweep_impl(h, model, mu, B, nt, 0, nt, dt, bdf, nullptr, nullptr, uN_out, nullptr, info, rt_stream(stream));
+}
+
+extern "C" int rt_online_sweep_segment_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt,
+                                           int64_t n0, int64_t n1, double dt, int bdf, double* Un, double* Unm1, double* uN_out,
+                                           int* info, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, uN_out && Un && Unm1);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    return sweep_impl(h, model, mu, B, nt, n0, n1, dt, bdf, Un, Unm1, uN_out, nullptr, info, rt_stream(stream));
 }
 
 extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model, const double* mu, int64_t B, int64_t nt,
@@ -1453,7 +1479,7 @@ extern "C" int rt_online_sweep_last_f64(rt_handle* h, const rt_rom_model* model,
     if (!h) return RT_EINVAL;
     RT_REQUIRE(h, uN_last);
     RT_CUDA(h, cudaSetDevice(h->device));
-    return sweep_impl(h, model, mu, B, nt, dt, bdf, nullptr, uN_last, info, rt_stream(stream));
+    return sweep_impl(h, model, mu, B, nt, 0, nt, dt, bdf, nullptr, nullptr, nullptr, uN_last, info, rt_stream(stream));
 }
 
 extern "C" int rt_online_step_f64(rt_handle* h, const rt_rom_model* model, const double* F, int64_t B, double dt, int bdf,

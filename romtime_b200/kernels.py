@@ -364,9 +364,9 @@ def online_step(dev_model, F, Un, Unm1, info, dt, bdf, step, Kadd=None, Madd=Non
     check(rc, h, "rt_online_step_f64")
 
 
-def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
-    """rt_online_sweep_f64 / rt_online_sweep_last_f64.  mus: (B, 3) [a0, omega, delta].
-    Returns (uN cuda tensor (B, nt, N) or (B, N), info int32 (B,))."""
+def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True, out=None):
+    """rt_online_sweep_f64 / rt_online_sweep_last_f64.  mus: (B, 3) [a0, omega, delta].  ``out``: optional preallocated
+    contiguous CUDA result tensor.  Returns (uN cuda tensor (B, nt, N) or (B, N), info int32 (B,))."""
     if not dev_model.has_evaluator:
         raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
     md = to_device(mus).contiguous()
@@ -376,58 +376,89 @@ def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True):
     h = handle(md.device.index)
     lib = load_library()
     with torch.cuda.device(md.device):
+        shape = (B, nt, N) if history else (B, N)
+        if out is not None and not (out.is_cuda and out.is_contiguous() and out.dtype == F64 and tuple(out.shape) == shape):
+            raise ValueError(f"out must be a contiguous float64 CUDA tensor of shape {shape}")
         if history:
-            out = torch.empty((B, nt, N), dtype=F64, device=md.device)
+            out = torch.empty(shape, dtype=F64, device=md.device) if out is None else out
             rc = lib.rt_online_sweep_f64(h, ctypes.byref(dev_model.struct), _ptr(md), B, nt, float(dt), int(bdf), _ptr(out),
                                          _ptr(info), stream_ptr())
         else:
-            out = torch.empty((B, N), dtype=F64, device=md.device)
+            out = torch.empty(shape, dtype=F64, device=md.device) if out is None else out
             rc = lib.rt_online_sweep_last_f64(h, ctypes.byref(dev_model.struct), _ptr(md), B, nt, float(dt), int(bdf),
                                               _ptr(out), _ptr(info), stream_ptr())
     check(rc, h, "rt_online_sweep_f64")
     return out, info
 
 
-def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=None):
-    """The sweep with the history delivered in (pinned) HOST memory: parameters are processed in the chunks the
-    library plans (rt_sweep_chunk); the device-to-host copy of chunk c runs on a side stream while chunk c + 1 is
-    computed, through two device staging buffers.  ``mus``: (B, 3) host array / tensor (pinned for an asynchronous
-    upload).  Returns (uN host tensor (B, nt, N), info int32 cuda tensor (B,))."""
+def online_sweep_segments(dev_model, mus, nt, dt, bdf=2, segment=100, out=None, on_segment=None):
+    """rt_online_sweep_segment_f64: the nt-step sweep in segments of ``segment`` steps with the state carried between
+    them (bit-identical to the uninterrupted sweep).  ``on_segment(n0, n1)`` is called after segment [n0, n1) has been
+    enqueued on the current stream.  Returns (uN cuda tensor (B, nt, N), info int32 (B,))."""
     if not dev_model.has_evaluator:
         raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
+    md = to_device(mus).contiguous()
+    B, N = md.shape[0], dev_model.N
+    if out is None:
+        out = torch.empty((B, nt, N), dtype=F64, device=md.device)
+    info = torch.empty(B, dtype=torch.int32, device=md.device)
+    Un = torch.empty((B, N), dtype=F64, device=md.device)
+    Unm1 = torch.empty((B, N), dtype=F64, device=md.device)
+    h = handle(md.device.index)
+    lib = load_library()
+    with torch.cuda.device(md.device):
+        for n0 in range(0, nt, segment):
+            n1 = min(nt, n0 + segment)
+            rc = lib.rt_online_sweep_segment_f64(h, ctypes.byref(dev_model.struct), _ptr(md), B, nt, n0, n1, float(dt), int(bdf),
+                                                 _ptr(Un), _ptr(Unm1), _ptr(out), _ptr(info), stream_ptr())
+            check(rc, h, "rt_online_sweep_segment_f64")
+            if on_segment is not None:
+                on_segment(n0, n1)
+    return out, info
+
+
+def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=None, segment=100):
+    """The sweep with the history delivered in (pinned) HOST memory.  The sweep runs in segments of ``segment`` time steps
+    (rt_online_sweep_segment_f64, state carried on the device); the finished time slab [:, n0:n1, :] of the device
+    history goes to the host as one strided copy (rt_memcpy2d_async) on a side stream while the next segment is
+    computed, so only the last slab's copy is exposed -- whatever the number of parameters per GPU.
+    ``mus``: (B, 3) host array / tensor (pinned for an asynchronous upload).
+    Returns (uN host tensor (B, nt, N), info int32 cuda tensor (B,))."""
     mh = mus if isinstance(mus, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(mus, dtype=np.float64))
     mh = mh.reshape(-1, 3)
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     B, N = mh.shape[0], dev_model.N
     if out_host is None:
-        out_host = torch.empty((B, nt, N), dtype=F64).pin_memory()
+        out_host = torch.empty((B, nt, N), dtype=F64, pin_memory=True)
+    if not (out_host.is_contiguous() and tuple(out_host.shape) == (B, nt, N)):
+        raise ValueError("out_host must be a contiguous (B, nt, N) host tensor")
     lib = load_library()
     h = handle(dev.index)
-    sms = torch.cuda.get_device_properties(dev).multi_processor_count
-    chunk = max(1, min(B, int(lib.rt_sweep_chunk(B, N, sms))))
-    info = torch.empty(B, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         main = torch.cuda.current_stream()
         side = torch.cuda.Stream()
-        bufs = [torch.empty((chunk, nt, N), dtype=F64, device=dev) for _ in range(2 if B > chunk else 1)]
-        copied = [None, None]
-        for c, p0 in enumerate(range(0, B, chunk)):
-            n = min(chunk, B - p0)
-            buf = bufs[c % len(bufs)]
-            if copied[c % 2] is not None:
-                main.wait_event(copied[c % 2])  # the staging buffer is free again
-            md = mh[p0:p0 + n].to(dev, non_blocking=True).contiguous()
-            rc = lib.rt_online_sweep_f64(h, ctypes.byref(dev_model.struct), _ptr(md), n, nt, float(dt), int(bdf), _ptr(buf),
-                                         _ptr(info[p0:p0 + n]), stream_ptr())
-            check(rc, h, "rt_online_sweep_f64")
-            done = torch.cuda.Event()
-            done.record(main)
-            side.wait_event(done)
-            with torch.cuda.stream(side):
-                out_host[p0:p0 + n].copy_(buf[:n], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(side)
-            copied[c % 2] = ev
+        md = mh.to(dev, non_blocking=True)
+        info = torch.empty(B, dtype=torch.int32, device=dev)
+        # the device history of a parameter block must fit next to the sweep's own scratch: blocks of at most a third of the free memory
+        free_bytes, _ = torch.cuda.mem_get_info(dev)
+        block = max(1, min(B, int(free_bytes // 3) // (nt * N * 8)))
+        pitch = nt * N * 8
+        for p0 in range(0, B, block):
+            nb = min(block, B - p0)
+            out = torch.empty((nb, nt, N), dtype=F64, device=dev)
+            host0 = out_host.data_ptr() + p0 * pitch
+
+            def ship(n0, n1, out=out, host0=host0, nb=nb):
+                done = torch.cuda.Event()
+                done.record(main)
+                side.wait_event(done)
+                rc = lib.rt_memcpy2d_async(h, c_vp(host0 + n0 * N * 8), pitch, c_vp(out.data_ptr() + n0 * N * 8), pitch,
+                                           (n1 - n0) * N * 8, nb, 1, c_vp(side.cuda_stream))
+                check(rc, h, "rt_memcpy2d_async")
+
+            _, info_b = online_sweep_segments(dev_model, md[p0:p0 + nb], nt, dt, bdf=bdf, segment=segment, out=out, on_segment=ship)
+            info[p0:p0 + nb] = info_b
+            out.record_stream(side)
         main.wait_stream(side)
         side.synchronize()  # the history is in HOST memory: it must be complete when this returns
     return out_host, info

@@ -141,6 +141,30 @@ def test_sweep_multi_chunk_consistency():
     assert np.array_equal(hist[:, -1, :].numpy(), last)
 
 
+@pytest.mark.parametrize("N,m,B,nt,seg", [(64, 16, 300, 23, 5), (64, 128, 150, 12, 4), (20, 7, 40, 30, 7), (100, 9, 6, 9, 2)])
+def test_segmented_sweep_is_bitwise_the_uninterrupted_one(N, m, B, nt, seg):
+    """rt_online_sweep_segment_f64 carries the state (u_n, u_n-1, the accumulated time, the BDF start-up) from one
+    segment to the next: any segmentation reproduces the uninterrupted sweep bit for bit -- also what makes ten
+    100-step bench segments one 1000-step sweep.  The host-delivered form ships every finished time slab."""
+    import torch
+
+    from romtime_b200 import kernels
+
+    model = synthetic.make_piston_model(N=N, m=m, seed=N + 3)
+    mus = synthetic.sample_mus(B, seed=13)
+    dm = kernels.DeviceRomModel(model)
+    whole, info = kernels.online_sweep(dm, mus, nt, 1e-3, bdf=2)
+    seen = []
+    parts, info_s = kernels.online_sweep_segments(dm, mus, nt, 1e-3, bdf=2, segment=seg, on_segment=lambda a, b: seen.append((a, b)))
+    assert seen[0] == (0, seg) and seen[-1][1] == nt and all(x[1] == y[0] for x, y in zip(seen, seen[1:]))
+    assert torch.equal(whole, parts) and torch.equal(info, info_s)
+    host, _ = kernels.online_sweep_to_host(dm, mus, nt, 1e-3, bdf=2, segment=seg)
+    assert not host.is_cuda and torch.equal(host, whole.cpu())
+    b1, _ = kernels.online_sweep_segments(dm, mus, nt, 1e-3, bdf=1, segment=seg)
+    w1, _ = kernels.online_sweep(dm, mus, nt, 1e-3, bdf=1)
+    assert torch.equal(b1, w1)
+
+
 @pytest.mark.parametrize("N", [5, 32, 33, 40, 63, 64, 100])
 def test_dense_solve_needs_pivoting(N):
     """The per-parameter solver (LU for N <= 32 and N > 64, blocked Gauss-Jordan on DMMA tiles in between) must
