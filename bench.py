@@ -322,6 +322,53 @@ def c4_leg(a, torch, kernels, with_cpu):
     return res
 
 
+# ------------------------------------------------------------------------------- tree-walk leg
+def treewalk_leg(a, torch, with_cpu):
+    """How the reference really consumes orth (rom/rom.py:313-406, deim/deim.py:279-397): P per-parameter time-PODs with
+    tol-driven ragged widths, then the mu-POD of the stacked bases -- at C1/C2-like sizes, through the batched device path
+    (two host reads per batch), with the reference's CPU loop (one scipy gesvd per matrix) beside it."""
+    import numpy as np
+
+    from romtime_b200 import synthetic
+    from romtime_b200.rom.pod import orth, orth_batch
+
+    tol = 1.0 - 1e-8
+    res = {"tol": "1 - 1e-8 (energy)", "cases": []}
+    for P, Nh, nt in ((64, 1000, 250), (64, 100, 50)):
+        mats = [synthetic.treewalk_snapshots(Nh, nt, seed=p) for p in range(P)]
+
+        def walk():
+            per = orth_batch(mats, tol=tol)
+            return per, orth(np.hstack([q for q, _, _ in per]), tol=tol, normalize=False)
+
+        walk()
+        torch.cuda.synchronize()
+        best = None
+        for _ in range(3):
+            t0 = time.perf_counter()
+            per, (Q, s, e) = walk()
+            torch.cuda.synchronize()
+            w = (time.perf_counter() - t0) * 1e3
+            best = w if best is None else min(best, w)
+        case = {"parameters": P, "snapshots_per_parameter": [Nh, nt], "host_to_host_ms": best,
+                "widths_min_max": [int(min(q.shape[1] for q, _, _ in per)), int(max(q.shape[1] for q, _, _ in per))],
+                "final_modes": int(Q.shape[1])}
+        if with_cpu:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import romtime_oracle as orc_mod
+
+            t0 = time.perf_counter()
+            per_c = [orc_mod.orth(S, tol=tol) for S in mats]
+            Qc, sc, _ = orc_mod.orth(np.hstack([q for q, _, _ in per_c]), tol=tol, normalize=False)
+            case["cpu_loop_ms"] = (time.perf_counter() - t0) * 1e3
+            case["cpu_sample"] = f"oracle orth (rom/pod.py:7-62, scipy gesvd) per matrix + stacked mu-POD, {os.cpu_count()} host cores, BLAS default threads"
+            case["widths_equal_cpu"] = bool([q.shape[1] for q, _, _ in per] == [q.shape[1] for q, _, _ in per_c])
+            case["per_parameter_sigma_max_rel"] = float(max(np.max(np.abs(a_[1][: a_[0].shape[1]] - b_[1][: b_[0].shape[1]]) / b_[1][: b_[0].shape[1]])
+                                                            for a_, b_ in zip(per, per_c)))
+        res["cases"].append(case)
+    return res
+
+
 # ------------------------------------------------------------------------------- main arm
 def emit(line, fd):
     os.write(fd, (json.dumps(line) + "\n").encode())
@@ -575,6 +622,13 @@ def main():
         except Exception as exc:  # report, never hide
             c4 = {"error": repr(exc)}
 
+    tw = None
+    if not a.skip_pod and world == 1:
+        try:
+            tw = treewalk_leg(a, torch, not a.skip_cpu)
+        except Exception as exc:  # report, never hide
+            tw = {"error": repr(exc)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -587,7 +641,7 @@ def main():
                     "host_history_equals_device_history": e2e_matches},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_baseline,
             "parity_1000_steps": parity, "sweep_m16": m16,
-            "pod": pod, "mdeim_c4": c4, "certification": cert, "singular_solves": bad,
+            "pod": pod, "mdeim_c4": c4, "treewalk": tw, "certification": cert, "singular_solves": bad,
         }
         emit(line, out_fd)
     if world > 1:

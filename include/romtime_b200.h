@@ -249,6 +249,29 @@ int rt_profile_read(rt_handle* h, double* ms, int64_t* launches);
 /* number of kernels launched by this handle since creation (bench.py "gpu_launches") */
 int64_t rt_launch_count(const rt_handle* h);
 
+/* ---------------------------------------------- batched small POD (tree walk) ------------- */
+/* The reference consumes orth as many small per-parameter time-PODs followed by one stacked mu-POD (rom/rom.py:313-406,
+ * deim/deim.py:279-397, deim/nonlinear.py:435-466).  These two calls do the eigen-work of a whole BATCH of such PODs in
+ * one launch each (one CTA per problem, everything in shared memory, no host round trip inside); the Gram matrices and
+ * the lifts around them are the ordinary rt_pod_gram_f64 / rt_pod_lift_f64 launches, queued without synchronisation.
+ *
+ * rt_small_gram_eig_f64: problem p has the n_p x n_p Gram matrix G_all + p * stride_g (row-major, leading dimension
+ * n_p; n_of[p] = n_p <= nmax <= 256, device ints).  Out: w_all[p * nmax + k] eigenvalues descending (0 beyond the
+ * numerical rank: pivoted-Cholesky cut at 8 ulp of the largest diagonal entry, as rt_sym_eig_f64), W_all + p * stride_w
+ * the n_p x n_p row-major eigenvector matrix (vector k in column k, zero beyond the rank), rank[p], info[p]:
+ * 0 ok, 1 = numerical rank above 96 (use rt_sym_eig_f64 for this problem), 2 = Jacobi did not converge. */
+int rt_small_gram_eig_f64(rt_handle* h, const double* G_all, int64_t stride_g, const int* n_of, int64_t P,
+                          int64_t nmax, double* w_all, double* W_all, int64_t stride_w, int* rank, int* info,
+                          void* stream);
+/* rt_small_refine_f64: the Hestenes refinement step for a batch: H_p = Y_p^T Y_p (c_p x c_p row-major, leading dimension
+ * c_p, c_of[p] = c_p <= cmax <= 96) of lifted, nearly orthogonal graded columns -> all eigenpairs with small RELATIVE
+ * errors (Cholesky + one-sided Jacobi).  Out: lam_all[p * cmax + k] descending, X_all + p * stride_x (c_p x c_p row-major,
+ * vector k in column k), defect[p] = max |h_ij| / sqrt(h_ii h_jj) of the input, info[p]: 0 ok, 1 = H not positive
+ * definite (use rt_sym_eig_jacobi_f64), 2 = not converged. */
+int rt_small_refine_f64(rt_handle* h, const double* H_all, int64_t stride_h, const int* c_of, int64_t P,
+                        int64_t cmax, double* lam_all, double* X_all, int64_t stride_x, double* defect, int* info,
+                        void* stream);
+
 /* ---------------------------------------------- certification (rom/hrom.py:504-626) -------- */
 /* S-ROM error estimator of utils.compute_rom_difference (utils.py:173-212) for every (parameter, step) of a pair
  * of sweeps:  err[b*nt + n] = || V_srom (uN_srom[b, n, :] - pad(uN[b, n, :])) ||_2 / sqrt(Nh).

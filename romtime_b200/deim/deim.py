@@ -19,7 +19,7 @@ import numpy as np
 
 from ..conventions import EmpiricalInterpolation, RomParameters, Stage
 from ..rom.base import Reductor
-from ..rom.pod import orth
+from ..rom.pod import orth, orth_batch
 from ..utils import dump_pickle, functional_to_array, read_pickle
 
 
@@ -200,13 +200,17 @@ class DiscreteEmpiricalInterpolation(Reductor):
     def assemble_snapshot(self, mu, t):
         return self._assemble_functional(mu, t)
 
-    def walk_time(self, mu, ts, normalize=True, num=None, tol=None):
-        """Time branch: snapshots over ``ts`` for a frozen ``mu`` -> POD (never normalised, reference
-        deim/deim.py:355-398; MDEIM zeroes the boundary entry 0)."""
+    def _time_snapshots(self, mu, ts):
+        """Snapshots over ``ts`` for a frozen ``mu`` (reference deim/deim.py:378-388; MDEIM zeroes the boundary entry 0)."""
         snapshots = np.array([self.assemble_snapshot(mu, t) for t in ts]).T
         if self.TYPE == EmpiricalInterpolation.MDEIM:
             snapshots[0, :] = 0.0
-        return orth(snapshots=snapshots, num=num, tol=tol, normalize=False)
+        return snapshots
+
+    def walk_time(self, mu, ts, normalize=True, num=None, tol=None):
+        """Time branch: snapshots over ``ts`` for a frozen ``mu`` -> POD (never normalised, reference
+        deim/deim.py:355-398)."""
+        return orth(snapshots=self._time_snapshots(mu, ts), num=num, tol=tol, normalize=False)
 
     def tree_walk(self, ts, normalize=True, num_mu=None, num_t=None, tol_mu=None, tol_t=None,
                   num_snapshots=None, mu_space=None):
@@ -216,10 +220,15 @@ class DiscreteEmpiricalInterpolation(Reductor):
         off = self.report[Stage.OFFLINE]
         for key in (self.SPECTRUM_TIME, self.ENERGY_TIME, self.BASIS_TIME):
             off.setdefault(key, dict())
-        blocks = []
+        # the assemble callbacks run on the host, parameter after parameter (as in the reference); the per-parameter time-PODs
+        # (deim/deim.py:390-395) are independent of each other and go to the device as ONE batch (rom/pod.py orth_batch)
+        ids, snaps = [], []
         for mu in space:
             mu_idx, mu = self.add_mu(step=Stage.OFFLINE, mu=mu)
-            basis_t, sigmas_t, energy_t = self.walk_time(mu=mu, ts=ts, num=num_t, tol=tol_t, normalize=normalize)
+            ids.append(mu_idx)
+            snaps.append(self._time_snapshots(mu, ts))
+        blocks = []
+        for mu_idx, (basis_t, sigmas_t, energy_t) in zip(ids, orth_batch(snaps, num=num_t, tol=tol_t, normalize=False)):
             off[self.SPECTRUM_TIME][mu_idx] = sigmas_t
             off[self.ENERGY_TIME][mu_idx] = energy_t
             off[self.BASIS_TIME][mu_idx] = basis_t.shape[1]

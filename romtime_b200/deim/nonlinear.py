@@ -8,7 +8,7 @@ import numpy as np
 
 from ..conventions import EmpiricalInterpolation, RomParameters, Stage, Treewalk
 from ..rom.base import Reductor
-from ..rom.pod import orth
+from ..rom.pod import orth, orth_batch
 from ..utils import bilinear_to_csr, eliminate_zeros, vector_to_csr
 from .mdeim import MatrixDiscreteEmpiricalInterpolation, _sorted_topology
 
@@ -83,13 +83,17 @@ class MatrixDiscreteEmpiricalInterpolationNonlinear(MatrixDiscreteEmpiricalInter
     def walk_time(self, mu, ts, normalize=True, num_t=None, tol_t=None, num_basis=None, tol_basis=None):
         """Time branch with an inner POD over the linearisation functions at every instant, then a POD of
         the stacked per-instant bases (reference deim/nonlinear.py:399-466)."""
+        return orth(snapshots=self._instant_bases(mu, ts, normalize, num_t, tol_t), num=num_t, tol=tol_t, normalize=normalize)
+
+    def _instant_bases(self, mu, ts, normalize, num_t, tol_t):
+        """Inner level of the walk (deim/nonlinear.py:435-458): one POD over the linearisation functions per instant --
+        independent problems, one device batch -- stacked side by side."""
         per_instant = []
         for t in ts:
             snaps = np.array([self.assemble_snapshot(mu=mu, t=t, u_n=self.u_n[:, k]) for k in range(self.u_n.shape[1])]).T
             snaps[0, :] = 0.0
-            phi_psi, _, _ = orth(snapshots=snaps, num=num_t, tol=tol_t, normalize=normalize)
-            per_instant.append(phi_psi)
-        return orth(snapshots=np.hstack(per_instant), num=num_t, tol=tol_t, normalize=normalize)
+            per_instant.append(snaps)
+        return np.hstack([b for b, _, _ in orth_batch(per_instant, num=num_t, tol=tol_t, normalize=normalize)])
 
     def tree_walk(self, ts, normalize=True, num_mu=None, num_t=None, num_basis=None, tol_mu=None, tol_t=None,
                   tol_basis=None, num_snapshots=None, mu_space=None):
@@ -98,10 +102,15 @@ class MatrixDiscreteEmpiricalInterpolationNonlinear(MatrixDiscreteEmpiricalInter
         off = self.report[Stage.OFFLINE]
         for key in (self.SPECTRUM_TIME, self.ENERGY_TIME, self.BASIS_TIME):
             off.setdefault(key, dict())
-        blocks = []
+        # three levels (deim/nonlinear.py:367-397, :435-466): per instant (batched inside _instant_bases), per parameter
+        # (one batch over the parameters), then the mu-POD of the stacked bases
+        ids, stacks = [], []
         for mu in space:
             mu_idx, mu = self.add_mu(step=Stage.OFFLINE, mu=mu)
-            basis_t, sigmas_t, energy_t = self.walk_time(mu=mu, ts=ts, num_t=num_t, tol_t=tol_t, normalize=normalize)
+            ids.append(mu_idx)
+            stacks.append(self._instant_bases(mu, ts, normalize, num_t, tol_t))
+        blocks = []
+        for mu_idx, (basis_t, sigmas_t, energy_t) in zip(ids, orth_batch(stacks, num=num_t, tol=tol_t, normalize=normalize)):
             off[self.SPECTRUM_TIME][mu_idx] = sigmas_t
             off[self.ENERGY_TIME][mu_idx] = energy_t
             off[self.BASIS_TIME][mu_idx] = basis_t.shape[1]

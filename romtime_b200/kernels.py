@@ -188,6 +188,43 @@ def sym_eig_jacobi(H):
     return w, W, int(info.item()), float(defect.item())
 
 
+SMALL_NMAX, SMALL_RMAX = 256, 96  # limits of the batched small-POD kernels (include/romtime_b200.h)
+
+
+def small_gram_eig(G_all, n_of, nmax):
+    """rt_small_gram_eig_f64 for a batch of Gram matrices packed in G_all (P x nmax*nmax).  Returns device tensors
+    (w_all P x nmax, W_all P x nmax*nmax, rank P, info P); nothing is synchronised."""
+    P = G_all.shape[0]
+    dev = G_all.device
+    w_all = torch.empty((P, nmax), dtype=F64, device=dev)
+    W_all = torch.empty((P, nmax * nmax), dtype=F64, device=dev)
+    rank = torch.empty(P, dtype=torch.int32, device=dev)
+    info = torch.empty(P, dtype=torch.int32, device=dev)
+    h = handle(dev.index)
+    with torch.cuda.device(dev):
+        rc = load_library().rt_small_gram_eig_f64(h, _ptr(G_all), nmax * nmax, _ptr(n_of), P, nmax, _ptr(w_all), _ptr(W_all),
+                                                  nmax * nmax, _ptr(rank), _ptr(info), stream_ptr())
+    check(rc, h, "rt_small_gram_eig_f64")
+    return w_all, W_all, rank, info
+
+
+def small_refine(H_all, c_of, cmax):
+    """rt_small_refine_f64 for a batch of refinement Gram matrices packed in H_all (P x cmax*cmax).  Returns device
+    tensors (lam_all P x cmax, X_all P x cmax*cmax, defect P, info P); nothing is synchronised."""
+    P = H_all.shape[0]
+    dev = H_all.device
+    lam_all = torch.zeros((P, cmax), dtype=F64, device=dev)
+    X_all = torch.zeros((P, cmax * cmax), dtype=F64, device=dev)
+    defect = torch.zeros(P, dtype=F64, device=dev)
+    info = torch.empty(P, dtype=torch.int32, device=dev)
+    h = handle(dev.index)
+    with torch.cuda.device(dev):
+        rc = load_library().rt_small_refine_f64(h, _ptr(H_all), cmax * cmax, _ptr(c_of), P, cmax, _ptr(lam_all), _ptr(X_all),
+                                                cmax * cmax, _ptr(defect), _ptr(info), stream_ptr())
+    check(rc, h, "rt_small_refine_f64")
+    return lam_all, X_all, defect, info
+
+
 # ------------------------------------------------------------------ projections onto the reduced basis
 def project_vec(V, U):
     """rt_project_vec_f64: DEIM.project_basis, out (N x m) = V^T U."""

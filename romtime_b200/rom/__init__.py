@@ -1,6 +1,6 @@
 """POD + reduced-order model constructors (reference rom/__init__.py)."""
 from .base import Reductor
-from .pod import orth
+from .pod import orth, orth_batch
 from .rom import PistonEvaluator, RomConstructor, RomConstructorMoving, RomConstructorNonlinear
 
-__all__ = ["Reductor", "RomConstructor", "RomConstructorMoving", "RomConstructorNonlinear", "PistonEvaluator", "orth"]
+__all__ = ["Reductor", "RomConstructor", "RomConstructorMoving", "RomConstructorNonlinear", "PistonEvaluator", "orth", "orth_batch"]

@@ -209,6 +209,99 @@ def orth_device(S, num=None, tol=None, normalize=True, allreduce=None, deflate=T
     return Q, s, energy, VT, info
 
 
+def orth_device_batch(mats, num=None, tol=None, normalize=True):
+    """The same POD for a BATCH of small snapshot matrices (the per-parameter time-PODs of a tree walk), with the host
+    out of the inner loop: the Gram matrices and lifts of all problems are queued back to back, the eigen-work of the
+    whole batch is two launches (rt_small_gram_eig_f64, rt_small_refine_f64: one CTA per problem), and the host reads
+    spectra twice per BATCH instead of ~5 times per matrix.  Same algorithm and decisions as ``orth_device`` (Gram ->
+    eigensolve -> lift of the wanted + guard modes -> Hestenes refinement); any problem outside the fast path's limits
+    (more than 256 snapshots, numerical rank or candidate count above 96, a truncation rule that reaches below the
+    first Gram matrix's floor, a refinement that needs a second pass) goes through ``orth_device`` unchanged.
+    Returns a list of (Q cuda Nh x r, s numpy, energy numpy)."""
+    P = len(mats)
+    out = [None] * P
+    Sd = [kernels.to_device(S) for S in mats]
+    default_rule = not tol and not num
+    fast = [i for i in range(P) if Sd[i].dim() == 2 and 1 <= Sd[i].shape[1] <= kernels.SMALL_NMAX and Sd[i].shape[0] >= 1]
+    if len(fast) >= 2:
+        dev = Sd[fast[0]].device
+        nmax = max(Sd[i].shape[1] for i in fast)
+        G_all = torch.zeros((len(fast), nmax * nmax), dtype=torch.float64, device=dev)
+        cns = {}
+        for j, i in enumerate(fast):
+            G, cn = kernels.pod_gram(Sd[i], normalize=bool(normalize))
+            n = Sd[i].shape[1]
+            G_all[j, : n * n] = G.reshape(-1)
+            cns[i] = cn
+        n_of = torch.tensor([Sd[i].shape[1] for i in fast], dtype=torch.int32).to(dev)
+        w_all, W_all, rank_d, info_d = kernels.small_gram_eig(G_all, n_of, nmax)
+        w_h, rank_h, info_h = w_all.cpu().numpy(), rank_d.cpu().numpy(), info_d.cpu().numpy()   # host read 1 of 2
+        plan = []  # (slot, problem, s_tail, rank, want, c, Y)
+        for j, i in enumerate(fast):
+            Nh, n = Sd[i].shape
+            k = min(Nh, n)
+            if info_h[j] != 0:
+                continue
+            s_tail = np.sqrt(np.maximum(w_h[j, :k], 0.0))
+            rank = int(np.count_nonzero(s_tail > 0.0))
+            want = min(max(int(np.count_nonzero(_truncation(s_tail, _energy(s_tail), num, tol))), 0), rank)
+            if want > 0 and rank < k:
+                want = max(1, min(want, int(np.count_nonzero(s_tail >= DELIVER_FLOOR * s_tail[0]))))
+            if want == 0:
+                continue
+            c = _guard_width(s_tail, want, rank)
+            if c > kernels.SMALL_RMAX:
+                continue
+            W = W_all[j, : n * n].reshape(n, n)
+            Wc = W[:, :c].contiguous()
+            Wl = (Wc / cns[i][:, None]).contiguous() if normalize else Wc
+            Y = kernels.pod_lift(Sd[i], Wl, order="F")
+            plan.append([j, i, s_tail, rank, want, c, Y])
+        if plan:
+            cmax = max(pl[5] for pl in plan)
+            H_all = torch.zeros((len(plan), cmax * cmax), dtype=torch.float64, device=dev)
+            for jj, pl in enumerate(plan):
+                H = kernels.pod_gram(pl[6], normalize=False)[0]
+                H_all[jj, : pl[5] * pl[5]] = H.reshape(-1)
+            c_of = torch.tensor([pl[5] for pl in plan], dtype=torch.int32).to(dev)
+            lam_all, X_all, defect_d, info2_d = kernels.small_refine(H_all, c_of, cmax)
+            lam_h, defect_h, info2_h = lam_all.cpu().numpy(), defect_d.cpu().numpy(), info2_d.cpu().numpy()   # host read 2 of 2
+            for jj, (j, i, s_tail, rank, want, c, Y) in enumerate(plan):
+                if info2_h[jj] != 0 or c * defect_h[jj] > 0.1:
+                    continue   # needs a second rotation pass: general path
+                Nh, n = Sd[i].shape
+                k = min(Nh, n)
+                sc = np.sqrt(np.maximum(lam_h[jj, :c], 0.0))
+                s = s_tail.copy()
+                s[:c] = sc
+                energy = _energy(s)
+                r_total = int(np.count_nonzero(_truncation(s, energy, num, tol)))
+                floor_abs = RANK_FLOOR * s_tail[0]
+                if rank < k and (r_total > want or (default_rule and floor_abs > DROP_TOLERANCE)):
+                    continue   # the rule reaches below this Gram matrix's floor: deflated levels of the general path
+                keep = min(r_total, want)
+                inv = np.divide(1.0, sc[:keep], out=np.zeros(keep), where=sc[:keep] > 0)
+                X = X_all[jj, : c * c].reshape(c, c)
+                Xr = (X[:, :keep] * torch.as_tensor(inv, device=dev)).contiguous()
+                Q = kernels.pod_lift(Y, Xr, order="F")
+                out[i] = (Q, s, energy)
+    for i in range(P):
+        if out[i] is None:
+            Q, s, energy, _, _ = orth_device(Sd[i], num=num, tol=tol, normalize=normalize)
+            out[i] = (Q, s, energy)
+    return out
+
+
+def orth_batch(snapshots_list, num=None, tol=None, normalize=True):
+    """``[orth(S, num, tol, normalize) for S in snapshots_list]`` (reference rom/pod.py:7-62 per matrix) through the batched
+    device path -- what the tree walks call for their per-parameter time-PODs.  Returns a list of (Q, s, energy) NumPy."""
+    for S in snapshots_list:
+        if isinstance(S, list):
+            raise ValueError("You should use an array, not a list.")
+    res = orth_device_batch(list(snapshots_list), num=num, tol=tol, normalize=(normalize == True))  # noqa: E712
+    return [(Q.cpu().numpy(), s, energy) for Q, s, energy in res]
+
+
 def orth(snapshots, num=None, tol=None, normalize=True, return_VT=False):
     """Compute orthogonalization via SVD (reference rom/pod.py:7-62).
 

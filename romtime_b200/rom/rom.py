@@ -25,7 +25,7 @@ from ..base import RomBatchSolutions, RomSolutionsStorage
 from ..conventions import BDF, OperatorType, PistonParameters, RomParameters, Stage, Treewalk, TreewalkNonlinear
 from ..utils import bilinear_to_csr, function_to_array, functional_to_array, project_csr
 from .base import Reductor
-from .pod import orth
+from .pod import orth, orth_batch
 
 # device operator slots, in the order of rt_rom_model.ops (include/romtime_b200.h)
 _SLOTS = ("mass", "stiffness", "convection", "nonlinear_lifting", "trilinear", "rhs")
@@ -190,29 +190,35 @@ class RomConstructor(Reductor):
             fom.setup()
         off = self.report[Stage.OFFLINE]
         fom_solutions = dict()
-        blocks, blocks_nl = [], []
         tol_t = tolerances.get(RomParameters.TOL_TIME, None)
+        # the FOM solves stay on the host, parameter after parameter; the per-parameter time-PODs of the solution and of the
+        # nonlinear term (rom/rom.py:335, :349-351) are independent and go to the device as two batches after the loop
+        ids, snaps, snaps_nl_all = [], [], []
         for mu in space:
             mu_idx, mu = self.add_mu(mu=mu, step=Stage.OFFLINE)
             fom.setup()
             fom.update_parametrization(mu)
             fom.solve()
             fom_solutions[mu_idx] = fom.solutions.fom.copy()
-            basis_t, sig_t, en_t = orth(fom.solutions.snapshots, tol=tol_t)
+            ids.append(mu_idx)
+            snaps.append(np.array(fom.solutions.snapshots, dtype=float, copy=True))
+            # nonlinear term: drop the zero initial snapshot, boundary row does not matter
+            snaps_nl = np.array(fom.nonlinear_snapshots[1:]).T
+            snaps_nl[0, :] = 0.0
+            snaps_nl_all.append(snaps_nl)
+            if getattr(fom, "RUNTIME_PROCESS", False):
+                fom.save_probes(name=f"probes_offline_fom_{mu_idx}.csv")
+        blocks, blocks_nl = [], []
+        for mu_idx, (basis_t, sig_t, en_t), (basis_nl, sig_nl, en_nl) in zip(ids, orth_batch(snaps, tol=tol_t),
+                                                                             orth_batch(snaps_nl_all, tol=tol_t)):
             blocks.append(basis_t)
             off[Treewalk.SPECTRUM_TIME][mu_idx] = sig_t
             off[Treewalk.ENERGY_TIME][mu_idx] = en_t
             off[Treewalk.BASIS_TIME][mu_idx] = basis_t.shape[1]
-            # nonlinear term: drop the zero initial snapshot, boundary row does not matter
-            snaps_nl = np.array(fom.nonlinear_snapshots[1:]).T
-            snaps_nl[0, :] = 0.0
-            basis_nl, sig_nl, en_nl = orth(snaps_nl, tol=tol_t)
             blocks_nl.append(basis_nl)
             off[TreewalkNonlinear.SPECTRUM_TIME][mu_idx] = sig_nl
             off[TreewalkNonlinear.ENERGY_TIME][mu_idx] = en_nl
             off[TreewalkNonlinear.BASIS_TIME][mu_idx] = basis_t.shape[1]  # sic (reference rom/rom.py:363-365)
-            if getattr(fom, "RUNTIME_PROCESS", False):
-                fom.save_probes(name=f"probes_offline_fom_{mu_idx}.csv")
         stacked, stacked_nl = np.hstack(blocks), np.hstack(blocks_nl)
         off[Treewalk.BASIS_AFTER_WALK] = stacked.shape[1]
         off[TreewalkNonlinear.BASIS_AFTER_WALK] = stacked_nl.shape[1]

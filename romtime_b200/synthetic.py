@@ -101,6 +101,25 @@ def pod_snapshots(Nh, n, seed=1003, modes=256, decay=32.0, noise=1e-13, order="C
     return np.asfortranarray(S) if order == "F" else np.ascontiguousarray(S)
 
 
+def treewalk_snapshots(Nh, nt, seed=0, modes=24, decay=2.5, noise=1e-12):
+    """Time snapshots of ONE parameter of a tree walk at the reference's own sizes (C1/C2: Nh = 100-1000 dofs, nt = 10-250
+    instants): a smooth moving-domain field u(x, t; mu) = sum_k sigma_k sin((k+1) pi x + a_k) cos((k+1) w t + b_k) / L(t),
+    L(t) = 1 - delta (1 - cos w t), mu = (a0, w, delta) drawn from the piston box by ``seed``, plus round-off-level noise.
+    Numerical rank ~ 20-60, so tol-driven truncation gives ragged widths across parameters."""
+    rng = np.random.default_rng(1000 + seed)
+    a0, om, de = MU_LO + (MU_HI - MU_LO) * rng.random(3)
+    x = np.linspace(0.0, 1.0, Nh)[:, None]
+    t = np.linspace(0.0, 1.0, nt)[None, :]
+    L = 1.0 - de * (1.0 - np.cos(om * t))
+    k = np.arange(modes)
+    sig = 10.0 ** (-k / decay)
+    pa, pb = rng.random(modes) * np.pi, rng.random(modes) * 2.0 * np.pi
+    S = np.zeros((Nh, nt))
+    for j in range(modes):
+        S += sig[j] * np.sin((j + 1) * np.pi * x + pa[j]) * np.cos((j + 1) * om * t / 5.0 + pb[j])
+    return S / L + noise * rng.standard_normal((Nh, nt))
+
+
 def mdeim_snapshots(nnz, n, seed=1004, order="F"):
     """C4-style MDEIM snapshots: vectorised non-zeros of a tridiagonal-like operator,
     a_k(mu,t) = c0 + c1 L + c2 / L + c3 L'/L + c4 sin(w t + psi_k); every off-diagonal

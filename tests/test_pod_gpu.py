@@ -160,3 +160,82 @@ def test_sym_eig_jacobi_relative_accuracy(n):
     assert np.max(np.abs(X.T @ X - np.eye(n))) < 1e-12
     if n > 1:
         assert 0 < defect < 1e-2
+
+
+def _smooth_snapshots(Nh, n, seed, modes=18, decay=2.5, noise=1e-13):
+    rng = np.random.default_rng(seed)
+    x = np.linspace(0.0, 1.0, Nh)[:, None]
+    tt = np.linspace(0.0, 1.0, n)[None, :]
+    S = sum(10.0 ** (-k / decay) * np.sin((k + 1) * np.pi * x + rng.random()) * np.cos((k + 1) * 3.0 * tt + rng.random() * 6)
+            for k in range(modes))
+    return S + noise * rng.standard_normal((Nh, n))
+
+
+@pytest.mark.parametrize("kw", [dict(tol=1.0 - 1e-8), dict(num=6), dict(tol=1.0 - 1e-6, normalize=False), dict(num=9, normalize=False)])
+def test_orth_batch_matches_gesvd_per_matrix(kw):
+    """The batched tree-walk path (rt_small_gram_eig_f64 + rt_small_refine_f64, two host reads per BATCH): ragged sizes,
+    tol-driven ragged widths, and two members that must fall back to the general path (300 snapshots; numerical rank above
+    96).  Every member against the reference's per-matrix gesvd at 1e-10."""
+    from romtime_b200.rom.pod import orth_batch
+
+    mats = [_smooth_snapshots(Nh, n, seed) for seed, (Nh, n) in enumerate([(100, 50), (1000, 250), (400, 10), (333, 77), (64, 64), (2000, 128)])]
+    mats.append(np.asfortranarray(_smooth_snapshots(500, 120, 17)))                       # F-order member (np.array(list).T)
+    mats.append(_smooth_snapshots(700, 300, 18))                                          # more than 256 snapshots: general path
+    mats.append(np.random.default_rng(19).standard_normal((400, 150)))                    # full numerical rank: general path
+    res = orth_batch(mats, **kw)
+    assert len(res) == len(mats)
+    for S, (Q, s, energy) in zip(mats, res):
+        Qr, sr, er = orc.orth(S, **kw)
+        check_orth_result(Q, s, energy, None, Qr, sr, er)
+
+
+def test_small_eig_kernels_against_lapack():
+    """rt_small_gram_eig_f64 / rt_small_refine_f64 on their own: eigenvalues to a small relative error, orthonormal vectors."""
+    import torch
+
+    from romtime_b200 import kernels
+
+    rng = np.random.default_rng(3)
+    sizes = [7, 64, 200, 256]
+    nmax = max(sizes)
+    G_all = torch.zeros((len(sizes), nmax * nmax), dtype=torch.float64, device="cuda")
+    Gs = []
+    for j, n in enumerate(sizes):
+        X = rng.standard_normal((n + 40, min(n, 30))) * 10.0 ** (-np.arange(min(n, 30)) / 4.0)
+        A = X @ rng.standard_normal((min(n, 30), n))
+        G = A.T @ A
+        Gs.append(G)
+        G_all[j, : n * n] = torch.from_numpy(G.reshape(-1)).cuda()
+    n_of = torch.tensor(sizes, dtype=torch.int32, device="cuda")
+    w_all, W_all, rank, info = kernels.small_gram_eig(G_all, n_of, nmax)
+    assert not info.any().item()
+    for j, n in enumerate(sizes):
+        r = int(rank[j].item())
+        w = w_all[j, :n].cpu().numpy()
+        W = W_all[j, : n * n].reshape(n, n).cpu().numpy()
+        ref = np.linalg.eigvalsh(Gs[j])[::-1]
+        assert 0 < r <= min(n, 30) and np.all(w[r:] == 0.0)
+        assert np.max(np.abs(w[:r] - ref[:r])) <= 1e-13 * ref[0]
+        assert np.max(np.abs(W[:, :r].T @ W[:, :r] - np.eye(r))) < 1e-11
+        assert np.max(np.abs((W[:, :r] * w[:r]) @ W[:, :r].T - Gs[j])) < 1e-13 * ref[0]
+    # refinement: Gram matrix of nearly orthogonal graded columns -> every eigenvalue to a small RELATIVE error
+    cs = [5, 40, 96]
+    cmax = max(cs)
+    H_all = torch.zeros((len(cs), cmax * cmax), dtype=torch.float64, device="cuda")
+    Hs = []
+    for j, c in enumerate(cs):
+        Qo, _ = np.linalg.qr(rng.standard_normal((300, c)))
+        Y = (Qo + 1e-4 * rng.standard_normal((300, c))) * 10.0 ** (-np.arange(c) / 8.0)
+        H = Y.T @ Y
+        Hs.append((H, Y))
+        H_all[j, : c * c] = torch.from_numpy(H.reshape(-1)).cuda()
+    lam_all, X_all, defect, info2 = kernels.small_refine(H_all, torch.tensor(cs, dtype=torch.int32, device="cuda"), cmax)
+    assert not info2.any().item()
+    for j, c in enumerate(cs):
+        H, Y = Hs[j]
+        lam = lam_all[j, :c].cpu().numpy()
+        X = X_all[j, : c * c].reshape(c, c).cpu().numpy()
+        sv = np.linalg.svd(Y, compute_uv=False)
+        assert np.max(np.abs(np.sqrt(lam) - sv) / sv) < 1e-12          # relative, on a spectrum spanning 1e-12
+        assert np.max(np.abs(X.T @ X - np.eye(c))) < 1e-13
+        assert 1e-5 < float(defect[j].item()) < 1e-2
