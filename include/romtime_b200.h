@@ -172,8 +172,15 @@ typedef struct {
 } rt_rom_operator;
 
 /* RomConstructorNonlinear model (rom/rom.py:877-929).  ops order: mass, stiffness, convection,
- * nonlinear_lifting, trilinear, rhs.  evaluator: 0 = piston "rest", 1 = piston "sudden"
- * (problems/piston.py:18-60). */
+ * nonlinear_lifting, trilinear, rhs.  evaluator (the closed-form features phi(mu, t) of the device sampled-entry
+ * evaluator, entries = C phi + b0 T u*; tables from romtime_b200/evaluators.py):
+ *   0 = piston "rest", 1 = piston "sudden" (problems/piston.py:18-60), mu rows (a0, omega, delta):
+ *       phi = [1, L, 1/L, L', a0, b0 bL, bL' L, b0 bL^2, a0 bL, L' bL, bL/L, b0]   (fom/nonlinear.py:374-581)
+ *   2 = MFP1 heat problem on L(t) = 1 - sin(omega t) (problems/mfp1.py:27-75; omega = 0: fixed domain), mu rows
+ *       (delta, beta, alpha_0, omega), E = exp(-beta t):
+ *       phi = [1, L, alpha_0/L, L', beta E L, beta E delta^2 L^3, alpha_0 (1-E) delta^2 L, (1-E) delta^2 L' L^2, 0, 0, 0, 0]
+ *       (fom/heat.py:80-297, fom/base.py:377-495)
+ * n_mu: doubles per row of the sweep's mu array (0 means 3). */
 typedef struct {
     int32_t N;
     int32_t n_ops; /* 6 */
@@ -182,11 +189,13 @@ typedef struct {
                          * tables; consecutive calls with a bitwise-identical rt_rom_model (same id, same pointers)
                          * reuse the staged, PT_U^-1-folded operators kept in the handle.  Change the id whenever
                          * the CONTENTS behind the pointers change. */
+    int32_t n_mu;
+    int32_t reserved;
     rt_rom_operator ops[RT_MAX_OPS];
 } rt_rom_model;
 
 /* Batched RomConstructorNonlinear.solve: for every parameter b (mu[b, 0:3] = a0, omega, delta)
- * run nt implicit BDF steps from a zero initial condition (rom/rom.py:451-452):
+ * (n_mu doubles per row for the other evaluators) run nt implicit BDF steps from a zero initial condition (rom/rom.py:451-452):
  *   sampled entries -> theta -> K = bdf M + dt (A + C + N(u*) + N^) -> b = M w + dt f -> K u = b
  * (dense LU with partial pivoting replaces GMRES, rom/rom.py:36, :492).
  * bdf: 1 or 2.  uN_out: B x nt x N (row-major; [b][n][:] = reduced solution after step n).

@@ -40,6 +40,8 @@ class RomModel(ctypes.Structure):
         ("n_ops", ctypes.c_int32),
         ("evaluator", ctypes.c_int32),
         ("generation", ctypes.c_int32),
+        ("n_mu", ctypes.c_int32),
+        ("reserved", ctypes.c_int32),
         ("ops", RomOperator * RT_MAX_OPS),
     ]
 

@@ -117,7 +117,7 @@ struct SweepPlan {
     int N, Npad, N2, ldk;       // ldk: row stride of K / M / basis_cat rows (even)
     int m[kNOps], mpad[kNOps], qoff[kNOps + 1];
     int Qmat, Qall;             // rows of the 5 matrix operators / all six (multiples of 16)
-    int evaluator;
+    int evaluator, n_mu;
     int Bc, Bcpad;              // parameters in this chunk / padded row stride of q-major buffers
     int ldu;                    // row stride of the state vectors Un / Unm1 (Npad internally, N for caller-owned state)
     int qsum;                   // sum of the unpadded m[i] (row length of caller-supplied sampled entries)
@@ -145,6 +145,18 @@ __device__ __forceinline__ void piston_features(int which, double a0, double om,
     phi[6] = dbL * L; phi[7] = b0 * bL * bL; phi[8] = a0 * bL; phi[9] = dL * bL; phi[10] = bL / L; phi[11] = b0;
 }
 
+// MFP1 heat problem (problems/mfp1.py:27-75): L = 1 - sin(omega t) (omega = 0: fixed domain), boundary data b0 = 1 - E,
+// bL = (1 - E)(1 + delta^2 L^2), forcing beta E (1 + delta^2 x^2) - 2 delta^2 alpha_0 (1 - E); the features the P1 weak forms
+// of fom/heat.py:80-297 and the lifting of fom/base.py:377-495 reduce to (romtime_b200/evaluators.py Mfp1P1)
+__device__ __forceinline__ void mfp1_features(double de, double be, double al, double om, double t, double* phi) {
+    double s, c;
+    sincos(om * t, &s, &c);
+    const double L = 1.0 - s, dL = -om * c, E = exp(-be * t), d2 = de * de;
+    phi[0] = 1.0; phi[1] = L; phi[2] = al / L; phi[3] = dL; phi[4] = be * E * L; phi[5] = be * E * d2 * L * L * L;
+    phi[6] = al * (1.0 - E) * d2 * L; phi[7] = (1.0 - E) * d2 * dL * L * L;
+    phi[8] = 0.0; phi[9] = 0.0; phi[10] = 0.0; phi[11] = 0.0;
+}
+
 // Phi[f][p], Ustar[p][j] = u* (rom.py:897-901), Wv[p][j] = BDF history vector (rom.py:919-925)
 __global__ void k_state(SweepPlan pl, const double* __restrict__ mu, double t, int have_prev, int bdf2,
                         const double* __restrict__ Un, const double* __restrict__ Unm1, double* __restrict__ Phi,
@@ -152,7 +164,9 @@ __global__ void k_state(SweepPlan pl, const double* __restrict__ mu, double t, i
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (mu && e < pl.Bc) {
         double phi[RT_NF];
-        piston_features(pl.evaluator, mu[e * 3 + 0], mu[e * 3 + 1], mu[e * 3 + 2], t, phi);
+        const double* m = mu + e * pl.n_mu;
+        if (pl.evaluator == 2) mfp1_features(m[0], m[1], m[2], m[3], t, phi);
+        else piston_features(pl.evaluator, m[0], m[1], m[2], t, phi);
 #pragma unroll
         for (int f = 0; f < RT_NF; ++f) Phi[(int64_t)f * pl.Bcpad + e] = phi[f];
     }
@@ -1188,7 +1202,8 @@ int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_ev
         return RT_OK;
     }
     sc->valid = false;
-    RT_REQUIRE(h, model->evaluator == 0 || model->evaluator == 1);
+    RT_REQUIRE(h, model->evaluator >= 0 && model->evaluator <= 2);
+    RT_REQUIRE(h, model->n_mu == 0 || model->n_mu == (model->evaluator == 2 ? 4 : 3));
     SweepPlan& pl = cx.pl;
     SweepBuffers& b = cx.b;
     memset(&pl, 0, sizeof(pl));
@@ -1198,6 +1213,7 @@ int sweep_setup(rt_handle* h, const rt_rom_model* model, int64_t B, bool need_ev
     pl.N2 = pl.N * pl.N;
     pl.ldk = (int)even64(pl.N2);
     pl.evaluator = model->evaluator;
+    pl.n_mu = model->n_mu ? model->n_mu : 3;
     int off = 0, msum = 0;
     for (int i = 0; i < kNOps; ++i) {
         const rt_rom_operator& op = model->ops[i];
@@ -1441,7 +1457,7 @@ int sweep_impl(rt_handle* h, const rt_rom_model* model, const double* mu, int64_
             RT_CUDA(h, cudaMemsetAsync(b.Un, 0, state_bytes, st));    // zero initial condition (rom.py:451-452)
             RT_CUDA(h, cudaMemsetAsync(b.Unm1, 0, state_bytes, st));  // uN_n1 = zeros, not None (rom.py:456-460)
         }
-        const double* mu_c = mu + p0 * 3;
+        const double* mu_c = mu + p0 * pl.n_mu;
         double t = t0;
         for (int64_t n = n0; n < n1; ++n) {
             t += dt;  // same accumulation as the reference loop (rom.py:476-479)

@@ -331,7 +331,9 @@ class DeviceRomModel:
                              "(the batched dense solve keeps one system per CTA in shared memory)")
         # unique id of this set of device tables: lets the library keep the staged, folded operators between calls
         DeviceRomModel._generation += 1
-        self.evaluator = 0 if model.get("which", "rest") == "rest" else 1
+        # device feature set of the sampled-entry evaluator (include/romtime_b200.h): piston rest / sudden, or MFP1
+        self.evaluator = int(model["evaluator_id"]) if model.get("evaluator_id") is not None else (0 if model.get("which", "rest") == "rest" else 1)
+        self.n_mu = 4 if self.evaluator == 2 else 3
         self._keep = []
         self.m = []
         self.has_evaluator = True
@@ -339,6 +341,7 @@ class DeviceRomModel:
         self.struct.N = self.N
         self.struct.n_ops = len(OPS)
         self.struct.evaluator = self.evaluator
+        self.struct.n_mu = self.n_mu
         self.struct.generation = DeviceRomModel._generation
         for i, name in enumerate(OPS):
             op = model.get(name)
@@ -401,12 +404,19 @@ def online_step(dev_model, F, Un, Unm1, info, dt, bdf, step, Kadd=None, Madd=Non
     check(rc, h, "rt_online_step_f64")
 
 
+def _mus_on_device(dev_model, mus):
+    md = to_device(mus).contiguous()
+    if md.dim() != 2 or md.shape[1] != dev_model.n_mu:
+        raise ValueError(f"mus must be (B, {dev_model.n_mu}) for this model's evaluator, got {tuple(md.shape)}")
+    return md
+
+
 def online_sweep(dev_model, mus, nt, dt, bdf=2, history=True, out=None):
     """rt_online_sweep_f64 / rt_online_sweep_last_f64.  mus: (B, 3) [a0, omega, delta].  ``out``: optional preallocated
     contiguous CUDA result tensor.  Returns (uN cuda tensor (B, nt, N) or (B, N), info int32 (B,))."""
     if not dev_model.has_evaluator:
         raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
-    md = to_device(mus).contiguous()
+    md = _mus_on_device(dev_model, mus)
     B = md.shape[0]
     N = dev_model.N
     info = torch.empty(B, dtype=torch.int32, device=md.device)
@@ -434,7 +444,7 @@ def online_sweep_segments(dev_model, mus, nt, dt, bdf=2, segment=100, out=None, 
     enqueued on the current stream.  Returns (uN cuda tensor (B, nt, N), info int32 (B,))."""
     if not dev_model.has_evaluator:
         raise _lib.RomtimeB200Error("this model has no device evaluator tables (C): use online_step with host-assembled entries")
-    md = to_device(mus).contiguous()
+    md = _mus_on_device(dev_model, mus)
     B, N = md.shape[0], dev_model.N
     if out is None:
         out = torch.empty((B, nt, N), dtype=F64, device=md.device)
@@ -462,7 +472,7 @@ def online_sweep_to_host(dev_model, mus, nt, dt, bdf=2, out_host=None, device=No
     ``mus``: (B, 3) host array / tensor (pinned for an asynchronous upload).
     Returns (uN host tensor (B, nt, N), info int32 cuda tensor (B,))."""
     mh = mus if isinstance(mus, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(mus, dtype=np.float64))
-    mh = mh.reshape(-1, 3)
+    mh = mh.reshape(-1, dev_model.n_mu)
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     B, N = mh.shape[0], dev_model.N
     if out_host is None:

@@ -35,11 +35,59 @@ class PistonEvaluator:
     """Closed-form sampled entries for the device sweep: for operator ``op`` the entries at the DEIM
     points are ``C[op] @ phi(mu, t)`` (+ ``b0 * T @ u*`` for the trilinear term), ``phi`` being the 12
     piston features of include/romtime_b200.h (RT_NF).  ``which`` = "rest" | "sudden"
-    (reference problems/piston.py:18-60)."""
+    (reference problems/piston.py:18-60).  ``from_mesh`` derives the tables from the P1 mesh, the sampled entries of the
+    attached reductors and the reduced basis (romtime_b200/evaluators.py) -- the device replacement of the per-step
+    ``assemble_local`` calls (fom/base.py:523-599)."""
+
+    evaluator_id = None                       # None: 0 / 1 by ``which``
+    mu_names = (PistonParameters.A0, PistonParameters.OMEGA, PistonParameters.DELTA)
 
     def __init__(self, tables, which="rest"):
         self.tables = tables  # {slot name: {"C": (m, 12) array, "T": (m, N) array or None}}
         self.which = which
+
+    @classmethod
+    def from_mesh(cls, rom, nx, L0=1.0, which="rest"):
+        from ..evaluators import PistonP1
+
+        return cls(_tables_from_p1(rom, PistonP1(nx, L0=L0, which=which)), which=which)
+
+
+class Mfp1Evaluator(PistonEvaluator):
+    """The same for the MFP1 heat problem on the fixed or moving domain (problems/mfp1.py:27-75; device feature set 2,
+    parameters (delta, beta, alpha_0, omega), omega = 0 on the fixed domain)."""
+
+    evaluator_id = 2
+    mu_names = ("delta", "beta", "alpha_0", "omega")
+
+    def __init__(self, tables):
+        super().__init__(tables, which="rest")
+
+    @classmethod
+    def from_mesh(cls, rom, nx, L0):
+        from ..evaluators import Mfp1P1
+
+        return cls(_tables_from_p1(rom, Mfp1P1(nx, L0)))
+
+
+def _tables_from_p1(rom, p1):
+    """{slot: {"C", "T"}} for every reductor attached to ``rom`` from the closed-form P1 tables of ``p1``; the sampled
+    entries are the reductors' own ``dofs`` ((i,) or (row, col) tuples, deim/deim.py:217-224, deim/mdeim.py:102-124)."""
+    out = {}
+    for name, red in rom._slot_reductors().items():
+        reds = [r for r in (red if isinstance(red, list) else [red]) if r]
+        if not reds:
+            continue
+        if name not in p1.OPS:
+            raise ValueError(f"the {type(p1).__name__} evaluator has no closed form for the operator slot {name!r}")
+        if len(reds) > 1:
+            raise ValueError("the closed-form evaluators take ONE right-hand-side reductor (forcing + lifting together)")
+        parts = [p1.tables(name, [tuple(d) for d in r.dofs], V=rom.basis) for r in reds]
+        tab = {"C": np.vstack([p["C"] for p in parts])}
+        if any("T" in p for p in parts):
+            tab["T"] = np.vstack([p["T"] for p in parts])
+        out[name] = tab
+    return out
 
 
 def _is_sparse_like(op):
@@ -302,7 +350,8 @@ class RomConstructor(Reductor):
         hit = self._dev_model
         if hit is not None and len(hit[0]) == len(key) and all(a is b for a, b in zip(hit[0], key)):
             return hit[1]
-        model = {"N": self.N, "which": evaluator.which if evaluator else "rest"}
+        model = {"N": self.N, "which": evaluator.which if evaluator else "rest",
+                 "evaluator_id": getattr(evaluator, "evaluator_id", None)}
         for name in _SLOTS:
             red = slots[name]
             reds = [r for r in (red if isinstance(red, list) else [red]) if r]
@@ -435,8 +484,9 @@ class RomConstructor(Reductor):
 
     # ------------------------------------------------------------------ online: a batch of parameters
     def solve_batch(self, mus, evaluator, nt=None, dt=None, bdf=None, history=True, step=Stage.ONLINE, to_host=False):
-        """Sweep B parameters at once on the device.  ``mus``: (B, 3) array [a0, omega, delta] or a list
-        of mu dictionaries; ``evaluator``: a ``PistonEvaluator`` with the closed-form sampled-entry tables.
+        """Sweep B parameters at once on the device.  ``mus``: (B, n_mu) array in the evaluator's parameter order
+        ([a0, omega, delta] for the piston, [delta, beta, alpha_0, omega] for MFP1) or a list of mu dictionaries;
+        ``evaluator``: a ``PistonEvaluator`` / ``Mfp1Evaluator`` with the closed-form sampled-entry tables.
         Under ``torch.distributed`` every rank passes ITS shard of ``mus`` (see distributed.shard_range);
         there is no collective.  ``to_host=True`` delivers the history in pinned host memory, the copy of one chunk of
         parameters overlapping the sweep of the next (kernels.online_sweep_to_host).  Returns a ``RomBatchSolutions``."""
@@ -447,13 +497,13 @@ class RomConstructor(Reductor):
         dt = float(dt if dt is not None else fom.dt)
         if bdf is None:
             bdf = 2 if fom.BDF_SCHEME == BDF.TWO else 1
+        names = evaluator.mu_names
         if isinstance(mus, (list, tuple)) and mus and isinstance(mus[0], dict):
-            P = PistonParameters
-            arr = np.array([[m[P.A0], m[P.OMEGA], m[P.DELTA]] for m in mus], dtype=np.float64)
+            arr = np.array([[m.get(k, 0.0) for k in names] for m in mus], dtype=np.float64)
             mu_list = list(mus)
         else:
-            arr = np.asarray(mus, dtype=np.float64).reshape(-1, 3)
-            mu_list = [{PistonParameters.A0: r[0], PistonParameters.OMEGA: r[1], PistonParameters.DELTA: r[2]} for r in arr]
+            arr = np.asarray(mus, dtype=np.float64).reshape(-1, len(names))
+            mu_list = [dict(zip(names, r)) for r in arr]
         self.mu_space[step].extend(mu_list)  # one operation: add_mu's list.index per parameter is O(B^2)
         if mu_list:
             self.mu = mu_list[-1]

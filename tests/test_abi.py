@@ -33,7 +33,7 @@ def test_structs_match_header_layout():
     from romtime_b200 import _lib
 
     assert ctypes.sizeof(_lib.RomOperator) == 48
-    assert ctypes.sizeof(_lib.RomModel) == 16 + 8 * 48
+    assert ctypes.sizeof(_lib.RomModel) == 24 + 8 * 48  # N, n_ops, evaluator, generation, n_mu, reserved + RT_MAX_OPS operators
 
 
 def test_no_cpu_fallback():
