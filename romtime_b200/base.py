@@ -66,6 +66,33 @@ class RomBatchSolutions:
             raise ValueError("no reduced basis attached to this batch")
         return kernels.pod_lift(self._basis, kernels.to_device(self.rom_device[b]).t().contiguous(), order="C").cpu().numpy()
 
+    @property
+    def has_basis(self):
+        return self._basis is not None
+
+    def fom_batch(self, b0=0, b1=None, lifting=None):
+        """Lazy FOM reconstruction of parameters b0 .. b1 - 1 as ONE lift GEMM on the device (reference rom/rom.py:496-522
+        per step and parameter):  uc_h[b, n, :] = V uN[b, n, :] + g_h(mu_b, t_n).  ``lifting``: None (homogeneous part
+        only) or an evaluator from romtime_b200/evaluators.py (``PistonP1`` / ``Mfp1P1``) whose boundary lifting is a
+        combination of k fixed nodal shapes, g_h = coef(mu, t) @ shapes -- the coefficients ride along as k extra
+        columns of the GEMM's left operand.  Returns a CUDA tensor (b1 - b0, nt, Nh)."""
+        import torch
+
+        from . import kernels
+
+        if self._basis is None:
+            raise ValueError("no reduced basis attached to this batch")
+        b1 = len(self) if b1 is None else b1
+        u = kernels.to_device(self.rom_device[b0:b1])
+        nb, nt, N = u.shape
+        W = kernels.to_device(np.ascontiguousarray(np.asarray(self._basis).T))            # N x Nh
+        left = u.reshape(nb * nt, N)
+        if lifting is not None:
+            coef, shapes = lifting.lifting(self.mus[b0:b1], self.ts)                      # (nb, nt, k), (k, Nh)
+            left = torch.cat([left, kernels.to_device(coef).reshape(nb * nt, -1)], dim=1).contiguous()
+            W = torch.cat([W, kernels.to_device(shapes)], dim=0).contiguous()
+        return kernels.pod_lift(left, W, order="C").reshape(nb, nt, -1)
+
     def storage(self, b, domain=None, lifting=None):
         """A reference-style RomSolutionsStorage for parameter b."""
         fom = self.fom(b) if self._basis is not None else None

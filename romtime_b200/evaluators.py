@@ -161,6 +161,17 @@ class PistonP1:
                 raise KeyError(op)
         return {"C": C, "T": T} if T is not None else {"C": C}
 
+    def lifting(self, mus, ts):
+        """Boundary lifting at the mesh nodes as coef (B, nt, 1) @ shapes (1, Nh): g_h = bL(mu, t) x / L(t), and x / L is the
+        reference coordinate x0 / L0 on the scaled mesh (fom/nonlinear.py:119-150, rom/rom.py:505-522)."""
+        ts = np.asarray(ts, dtype=float)
+        coef = np.empty((len(mus), len(ts), 1))
+        for b, mu in enumerate(mus):
+            a0, om, de = (mu["a0"], mu["omega"], mu["delta"]) if isinstance(mu, dict) else mu
+            coef[b, :, 0] = -de * (om / a0) * (np.sin(om * ts) if self.which == "rest" else np.cos(om * ts))
+        x0 = self.ref.L0 * (self.ref.nx - np.arange(self.ref.Nh)) / self.ref.nx
+        return coef, (x0 / self.ref.L0)[None, :]
+
     # host restatement of the device features (k_state), for tests and for callers that want entries on the host
     def features(self, mu, t):
         a0, om, de = (mu["a0"], mu["omega"], mu["delta"]) if isinstance(mu, dict) else mu
@@ -208,6 +219,20 @@ class Mfp1P1:
             else:
                 raise KeyError(op)
         return {"C": C}
+
+    def lifting(self, mus, ts):
+        """g_h = bL x / L + b0 (L - x) / L at the nodes (fom/base.py:440-465) as coef (B, nt, 2) @ shapes (2, Nh):
+        shapes = [x0 / L0, 1 - x0 / L0], coef = [bL, b0] with bL = (1 - E)(1 + delta^2 L(t)^2 L0^2), b0 = 1 - E."""
+        ts = np.asarray(ts, dtype=float)
+        coef = np.empty((len(mus), len(ts), 2))
+        for b, mu in enumerate(mus):
+            de, be, al, om = (mu["delta"], mu["beta"], mu["alpha_0"], mu.get("omega", 0.0)) if isinstance(mu, dict) else mu
+            E = np.exp(-be * ts)
+            Lc = (1.0 - np.sin(om * ts)) * self.ref.L0
+            coef[b, :, 0] = (1.0 - E) * (1.0 + de * de * Lc * Lc)
+            coef[b, :, 1] = 1.0 - E
+        x0 = self.ref.L0 * (self.ref.nx - np.arange(self.ref.Nh)) / self.ref.nx
+        return coef, np.stack([x0 / self.ref.L0, 1.0 - x0 / self.ref.L0])
 
     def features(self, mu, t):
         de, be, al, om = (mu["delta"], mu["beta"], mu["alpha_0"], mu.get("omega", 0.0)) if isinstance(mu, dict) else mu

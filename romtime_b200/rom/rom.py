@@ -50,7 +50,10 @@ class PistonEvaluator:
     def from_mesh(cls, rom, nx, L0=1.0, which="rest"):
         from ..evaluators import PistonP1
 
-        return cls(_tables_from_p1(rom, PistonP1(nx, L0=L0, which=which)), which=which)
+        p1 = PistonP1(nx, L0=L0, which=which)
+        ev = cls(_tables_from_p1(rom, p1), which=which)
+        ev.p1 = p1      # also knows the boundary lifting at the nodes (RomBatchSolutions.fom_batch(lifting=ev.p1))
+        return ev
 
 
 class Mfp1Evaluator(PistonEvaluator):
@@ -67,7 +70,10 @@ class Mfp1Evaluator(PistonEvaluator):
     def from_mesh(cls, rom, nx, L0):
         from ..evaluators import Mfp1P1
 
-        return cls(_tables_from_p1(rom, Mfp1P1(nx, L0)))
+        p1 = Mfp1P1(nx, L0)
+        ev = cls(_tables_from_p1(rom, p1))
+        ev.p1 = p1
+        return ev
 
 
 def _tables_from_p1(rom, p1):

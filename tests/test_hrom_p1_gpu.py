@@ -67,8 +67,11 @@ def test_mfp1_moving_hrom_end_to_end():
     batch = rom.solve_batch([dict(m) for m in online], ev, nt=nt, dt=fom.dt, bdf=2)
     uN = batch.rom_device.cpu().numpy()
     assert not batch.info.any().item()
+    # lazy FOM reconstruction of the whole batch: ONE lift GEMM, the boundary lifting riding along (rom/rom.py:496-522)
+    full = batch.fom_batch(lifting=ev.p1).cpu().numpy()
     for b, mu in enumerate(online):
         assert rel(uN[b].T, traj[b][0]) < 1e-10
+        assert rel(full[b].T, traj[b][1]) < 1e-10
         # against the full-order model and the manufactured solution (discretisation error of nx = 60, nt = 100: ~5e-4)
         fom.update_parametrization(mu)
         fom.solve()
@@ -122,6 +125,25 @@ def test_piston_hrom_host_callbacks_vs_device_evaluator(which):
     assert not batch.info.any().item()
     for b in range(len(online)):
         assert rel(uN[b].T, traj[b]) < 1e-10
+    # on-disk: the batch as the reference's per-parameter RomSolutionsStorage pickles, FOM fields rebuilt by one GEMM per block
+    import pickle
+    import tempfile
+
+    from romtime_b200.storage import ResultTree
+
+    with tempfile.TemporaryDirectory() as tmp:
+        tree = ResultTree(tmp)
+        files = tree.dump_batch(batch, prefix="solutions_online", lifting=ev.p1)
+        tree.dump_mu_space(rom)
+        tree.dump_reduced_basis(rom)
+        tree.dump_collateral_bases(rom)
+        st = pickle.load(open(files[1], "rb"))
+        assert st.rom.shape == (rom.N, nt) and st.fom.shape == (nx + 1, nt) and st.mu["a0"] == online[1]["a0"]
+        rom.solve(mu=dict(online[1]), step="online")
+        assert rel(st.fom, np.array(rom.solutions.fom)) < 1e-10
+        fresh = rom.mdeim_Mh.copy()
+        tree.load_collateral_basis(fresh)
+        assert fresh.dofs == rom.mdeim_Mh.dofs and np.array_equal(fresh.PT_U, rom.mdeim_Mh.PT_U)
     # the hyper-reduced model follows the full-order one (N = 12 modes, trilinear term interpolated)
     fom.update_parametrization(online[0])
     fom.solve()
