@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 METRIC = "rom_param_timesteps_per_s"
 # dominant kernel's DRAM traffic per launch from the committed ncu capture of this round (K written once, M never stored)
 NCU_GEMM_PROFILE = "profiles/r2_sweep_ncu.md"
-NCU_GEMM_DRAM_BYTES_PER_14208 = 532.1e6
+NCU_GEMM_DRAM_BYTES_PER_14208 = 531.8e6  # 101.95 MB read + 429.86 MB written
 UNIT = "param*timesteps/s"
 
 
