@@ -57,6 +57,10 @@ int rt_version(void);
 int rt_create(int device, rt_handle** out);
 int rt_destroy(rt_handle* h);
 const char* rt_last_error(const rt_handle* h);
+/* Enable loads from buffers that live on device `peer` (peer memory over NVLink / NVSwitch): afterwards any S / A / B
+ * pointer of the GEMM-shaped calls below may be peer memory (e.g. a neighbour rank's snapshot columns, opened through
+ * CUDA IPC); outputs stay local.  Used by the column-sharded POD Gram. */
+int rt_enable_peer_access(rt_handle* h, int peer);
 /* measured FP64 DMMA peak of this device in TFLOP/s (register-resident mma.sync.m8n8k4.f64 loop);
  * synchronous.  Used as the roofline denominator of the FP64-bound kernels. */
 int rt_fp64_peak_tflops(rt_handle* h, double* tflops);

@@ -52,6 +52,7 @@ SIGNATURES = {
     "rt_create": (c_int, [c_int, ctypes.POINTER(c_vp)]),
     "rt_destroy": (c_int, [c_vp]),
     "rt_last_error": (ctypes.c_char_p, [c_vp]),
+    "rt_enable_peer_access": (c_int, [c_vp, c_int]),
     "rt_fp64_peak_tflops": (c_int, [c_vp, ctypes.POINTER(c_dbl)]),
     "rt_pod_gram_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_int, c_vp, c_vp, c_vp]),
     "rt_gram_cross_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_i64, c_vp]),

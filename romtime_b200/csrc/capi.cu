@@ -41,6 +41,22 @@ extern "C" const char* rt_last_error(const rt_handle* h) { return h ? h->err : "
 
 extern "C" int64_t rt_launch_count(const rt_handle* h) { return h ? h->launches : 0; }
 
+// Let kernels of this handle's device read buffers that live on `peer` (NVLink / NVSwitch peer memory, e.g. a neighbour
+// rank's snapshot columns opened through CUDA IPC): the column-sharded Gram blocks then pull their B operand tile by tile
+// with TMA over NVLink while the DMMAs run -- no staging copy, no send / receive.
+extern "C" int rt_enable_peer_access(rt_handle* h, int peer) {
+    if (!h) return RT_EINVAL;
+    RT_CUDA(h, cudaSetDevice(h->device));
+    if (peer == h->device) return RT_OK;
+    int can = 0;
+    RT_CUDA(h, cudaDeviceCanAccessPeer(&can, h->device, peer));
+    if (!can) return rt_fail(h, RT_EINVAL, "device %d cannot access device %d as a peer", h->device, peer);
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return RT_OK; }
+    RT_CUDA(h, e);
+    return RT_OK;
+}
+
 // Strided device-to-host / host-to-device copy on a stream (cudaMemcpy2DAsync): a time slab [:, n0:n1, :] of the sweep
 // history (B x nt x N) goes to pinned host memory as ONE copy while later steps are computed.
 extern "C" int rt_memcpy2d_async(rt_handle* h, void* dst, int64_t dst_pitch, const void* src, int64_t src_pitch, int64_t width_bytes,

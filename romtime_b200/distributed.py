@@ -5,8 +5,9 @@ One process per GPU (``torch.distributed``, backend ``nccl`` on the box, ``gloo`
 * online sweep -- the parameter batch is split into contiguous shards (``shard_range``); the model is
   replicated; there is NO data-path collective.
 * POD -- the snapshot COLUMNS are sharded: rank g owns ``S_g (Nh x n_g)``.  The Gram matrix is built
-  block-wise: panels travel round a ring (``batch_isend_irecv`` double-buffered against the block GEMMs,
-  NVLink 5 through the switch), rank g computes the blocks ``G[g, (g+h) % P]`` for the hops
+  block-wise: rank g PULLS the panel of partner (g + h) % P from the owner's memory (CUDA IPC mapping over NVSwitch,
+  ``gram_column_sharded_peer``; the round-1 ring of ``batch_isend_irecv`` panels is kept as ``gram_column_sharded*``)
+  while the previous block is multiplied, and computes the blocks ``G[g, (g+h) % P]`` for the hops
   ``h = 0 .. P//2`` only (symmetry: the other half is the transpose, written by the same rank so the
   assembled matrix is exactly symmetric; the antipodal block of an even world is split between the pair), writes them into a zero ``n x n`` buffer and one
   ``all_reduce(SUM)`` of G (134 MB at n = 4096) leaves the full Gram matrix on every rank.  Every entry
@@ -168,8 +169,116 @@ def gram_column_sharded_overlapped(S_local, n, block_ops=None, group=None):
     return G
 
 
+def _open_peer_panels(S_local, needed, group):
+    """CUDA-IPC views of the other ranks' snapshot columns (same node): every rank publishes the handle of its S_local
+    (torch.multiprocessing's reduction of a CUDA tensor), the needed ones are opened in place -- no copy."""
+    from torch.multiprocessing.reductions import reduce_tensor
+
+    from . import kernels
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    fn, args = reduce_tensor(S_local)
+    handles = [None] * world
+    dist.all_gather_object(handles, (fn, args), group=group)
+    peers = {}
+    local = S_local.device.index
+    for src in needed:
+        f, a = handles[src]
+        owner = int(a[6]) if not isinstance(a[6], torch.device) else a[6].index
+        kernels.enable_peer_access(owner, local)
+        # the IPC handle is opened with THIS rank's device current (argument 6 of rebuild_cuda_tensor is the device the storage
+        # is mapped under): the mapping then lives in the local context and the local kernels read it over NVLink; a mapping
+        # made under the owner's device is not reachable from this device's kernels
+        a = list(a)
+        a[6] = local
+        peers[src] = f(*a)
+    return peers
+
+
+class PeerPanels:
+    """The partners' snapshot columns of a column-sharded matrix, opened ONCE (handle exchange + cudaIpcOpenMemHandle cost a few
+    milliseconds of host time): pass it to ``gram_column_sharded_peer`` / ``orth_column_sharded`` for every decomposition of
+    the same resident buffers.  Collective: every rank constructs it at the same point."""
+
+    def __init__(self, S_local, group=None):
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        self.key = (S_local.data_ptr(), tuple(S_local.shape), tuple(S_local.stride()))
+        self.srcs = [(rank + h) % world for h in range(1, world // 2 + 1)]
+        self.peers = _open_peer_panels(S_local, self.srcs, group) if world > 1 else {}
+
+    def matches(self, S_local):
+        return self.key == (S_local.data_ptr(), tuple(S_local.shape), tuple(S_local.stride()))
+
+
+def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=False, panels=None):
+    """Same result as ``gram_column_sharded`` without a ring: rank g PULLS the columns of partner (g + h) % P straight from
+    the owner's memory (CUDA IPC mapping, NVSwitch: full bandwidth between any pair) into one of two local panel buffers on
+    a copy stream while block h - 1 is multiplied -- one transfer of each panel, no send / receive pairing, no transposing
+    staging copy (the panel keeps the owner's layout), hop 1 hidden behind the diagonal block.
+    ``direct=True``: no copy at all, the GEMM's TMA reads the B tiles from peer memory while the DMMAs run.  Measured
+    slower: a peer tile is not cached in the LOCAL L2, so every tile row of the block re-reads the panel over NVLink
+    (4 x 4.1 GB per hop at 8 GPUs, 346 ms against 279 ms for the ring at 2 GPUs); kept for the record and for small blocks."""
+    ops = block_ops or DeviceBlockOps()
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return gram_column_sharded(S_local, n, ops, group)
+    rank = dist.get_rank(group)
+    shards = column_shards(n, world)
+    lo, hi = shards[rank]
+    hops = world // 2
+    srcs = [(rank + h) % world for h in range(1, hops + 1)]
+    if panels is not None and not panels.matches(S_local):
+        raise ValueError("these PeerPanels were opened for another buffer")
+    peers = panels.peers if panels is not None else _open_peer_panels(S_local, srcs, group)
+    dev = S_local.device
+    G = torch.zeros((n, n), dtype=S_local.dtype, device=dev)
+    main = torch.cuda.current_stream(dev)
+    if direct:
+        G[lo:hi, lo:hi] = ops.gram(S_local)
+        for h, src in enumerate(srcs, start=1):
+            _cross_block(ops, G, S_local, peers[src], rank, src, shards, world % 2 == 0 and h == hops)
+    else:
+        side = torch.cuda.Stream(device=dev)
+        Nh = S_local.shape[0]
+        wmax = max(b - a for a, b in shards)
+        bufs = [torch.empty((Nh, wmax), dtype=S_local.dtype, device=dev) for _ in range(min(2, hops))]
+        ready, free = [None] * (hops + 1), [None] * len(bufs)
+
+        def pull(h):
+            src = srcs[h - 1]
+            w = shards[src][1] - shards[src][0]
+            slot = (h - 1) % len(bufs)
+            with torch.cuda.stream(side):
+                if free[slot] is not None:
+                    side.wait_event(free[slot])      # the block that used this buffer is done
+                bufs[slot][:, :w].copy_(peers[src], non_blocking=True)
+                ready[h] = torch.cuda.Event()
+                ready[h].record(side)
+
+        side.wait_stream(main)
+        pull(1)
+        G[lo:hi, lo:hi] = ops.gram(S_local)
+        for h, src in enumerate(srcs, start=1):
+            if h + 1 <= hops and len(bufs) > 1:
+                pull(h + 1)
+            main.wait_event(ready[h])
+            slot = (h - 1) % len(bufs)
+            w = shards[src][1] - shards[src][0]
+            _cross_block(ops, G, S_local, bufs[slot][:, :w], rank, src, shards, world % 2 == 0 and h == hops)
+            free[slot] = torch.cuda.Event()
+            free[slot].record(main)
+            if h + 1 <= hops and len(bufs) == 1:
+                pull(h + 1)
+    dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
+    # the partners read this rank's columns until THEIR pulls are done: the all-reduce orders that on the device (a rank
+    # joins it only after its own blocks); the IPC mappings are closed once this rank's work has drained as well
+    main.synchronize()
+    del peers
+    return G
+
+
 def orth_column_sharded(S_local, n, num=None, tol=None, normalize=True, block_ops=None, group=None,
-                        overlap=True):
+                        overlap=True, peer=False, events=None, panels=None):
     """Distributed ``orth`` (reference rom/pod.py:7-62) of a column-sharded snapshot matrix.
 
     Returns ``(Q, s, energy, VT)``: Q (Nh x r) and VT (r x n) as tensors on this rank's device (Q is
@@ -181,10 +290,18 @@ def orth_column_sharded(S_local, n, num=None, tol=None, normalize=True, block_op
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     lo, hi = shard_range(n, world, rank)
     Nh = S_local.shape[0]
-    gram = gram_column_sharded_overlapped if overlap else gram_column_sharded
-    G = gram(S_local, n, ops, group)
+    if peer or panels is not None:
+        G = gram_column_sharded_peer(S_local, n, ops, group, panels=panels)
+    else:
+        G = (gram_column_sharded_overlapped if overlap else gram_column_sharded)(S_local, n, ops, group)
+    if events is not None:   # (Gram blocks + all-reduce) | (eigensolve, lift, refinement): nested in ONE run
+        events.append(torch.cuda.Event(enable_timing=True))
+        events[-1].record()
     cn = ops.finalize(G, normalize)
     w, W = ops.eig(G)
+    if events is not None:
+        events.append(torch.cuda.Event(enable_timing=True))
+        events[-1].record()
     k = min(Nh, n)
     w_host = w[:k].cpu().numpy()
     s = np.sqrt(np.maximum(w_host, 0.0))
@@ -210,52 +327,90 @@ def orth_column_sharded(S_local, n, num=None, tol=None, normalize=True, block_op
 
 
 # ------------------------------------------------------------------------------- bench leg (N > 1)
-def bench_pod(a, Nh, n):
-    """C3 POD leg of bench.py under torchrun: column-sharded synthetic snapshots, device timing, max over
-    ranks.  Every rank generates the same low-rank factors from the same seed and keeps its columns."""
-    from . import kernels
-
-    world, rank = dist.get_world_size(), dist.get_rank()
-    dev = torch.device("cuda", torch.cuda.current_device())
-    lo, hi = shard_range(n, world, rank)
+def _bench_snapshots(Nh, n, lo, hi, dev, noise_seed):
+    """Columns [lo, hi) of the C3 family: low-rank graded part + 1e-13 noise, generated in row slabs.  The noise
+    is drawn for the FULL row and sliced, so any column range of the same matrix is reproduced bit for bit on every rank."""
     g = torch.Generator(device=dev).manual_seed(1003)
     k = 256
     R = torch.randn((k, n), dtype=torch.float64, device=dev, generator=g)[:, lo:hi].contiguous()
     sig = torch.pow(10.0, -torch.arange(k, dtype=torch.float64, device=dev) / 32.0)
     S = torch.empty((Nh, hi - lo), dtype=torch.float64, device=dev)
-    rows = 65536
-    gn = torch.Generator(device=dev).manual_seed(7919 + rank)
+    rows = 65536 if noise_seed is None else 8192
+    gn = torch.Generator(device=dev).manual_seed(7919)
     for r0 in range(0, Nh, rows):
         r1 = min(Nh, r0 + rows)
         L = torch.randn((r1 - r0, k), dtype=torch.float64, device=dev, generator=g) * sig
         S[r0:r1] = L @ R
-        S[r0:r1] += 1e-13 * torch.randn((r1 - r0, hi - lo), dtype=torch.float64, device=dev, generator=gn)
-    del L, R
+        if noise_seed is None:   # full-size timing leg: per-rank noise (not compared with anything)
+            S[r0:r1] += 1e-13 * torch.randn((r1 - r0, hi - lo), dtype=torch.float64, device=dev, generator=gn)
+        else:                    # same-input leg: the full row's noise, sliced
+            S[r0:r1] += 1e-13 * torch.randn((r1 - r0, n), dtype=torch.float64, device=dev, generator=gn)[:, lo:hi]
+    return S
+
+
+def bench_pod(a, Nh, n):
+    """C3 POD leg of bench.py under torchrun: column-sharded synthetic snapshots, device timing, max over ranks; the Gram
+    blocks read the partners' columns from peer memory (RT_POD_RING=1: the ring of send / receive panels instead).  A
+    reduced-row copy of the SAME matrix is also decomposed on a single GPU and compared with the sharded result."""
+    import os
+
+    from . import kernels
+    from .rom.pod import orth_device
+
+    world, rank = dist.get_world_size(), dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    lo, hi = shard_range(n, world, rank)
+    peer = os.environ.get("RT_POD_RING", "0") != "1"
+    # ---- same-input check at reduced Nh: sharded result against the single-GPU path on the identical matrix
+    Nh_s = min(Nh, 65536)
+    S_full = _bench_snapshots(Nh_s, n, 0, n, dev, noise_seed=1)
+    Q1, s1, _, _, _ = orth_device(S_full, num=64)
+    Qp, sp, _, _ = orth_column_sharded(S_full[:, lo:hi].contiguous(), n, num=64, peer=peer)
+    same = {"rows": Nh_s,
+            "sharded_vs_single_sigma_max_rel": float(np.max(np.abs(sp[:64] - s1[:64]) / s1[:64])),
+            "Q_subspace_max": float((Qp @ (Qp.t() @ Q1) - Q1).abs().max().item()),
+            "Q_columns_max_abs_1_minus_dot": float(((Qp * Q1).sum(dim=0).abs() - 1.0).abs().max().item())}
+    del S_full, Q1, Qp
+    torch.cuda.empty_cache()
+    # ---- full-size timing
+    S = _bench_snapshots(Nh, n, lo, hi, dev, noise_seed=None)
+    panels, t_map = None, 0.0
+    if peer:
+        import time
+
+        dist.barrier()
+        t0 = time.perf_counter()
+        panels = PeerPanels(S)            # one-off: handle exchange + IPC mapping of the partners' columns
+        dist.barrier()
+        t_map = (time.perf_counter() - t0) * 1e3
     best = None
     for it in range(3):
         dist.barrier()
         torch.cuda.synchronize()
-        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-        e[0].record()
-        G = gram_column_sharded_overlapped(S, n)
-        e[1].record()
-        del G
-        Q, s, energy, VT = orth_column_sharded(S, n, num=64)
-        e[2].record()
+        ev = [torch.cuda.Event(enable_timing=True)]
+        ev[0].record()
+        Q, s, energy, VT = orth_column_sharded(S, n, num=64, peer=peer, events=ev, panels=panels)
+        ev.append(torch.cuda.Event(enable_timing=True))
+        ev[-1].record()
         torch.cuda.synchronize()
-        t = torch.tensor([e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2])], dtype=torch.float64, device=dev)
+        t = torch.tensor([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]), ev[0].elapsed_time(ev[3])],
+                         dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t = t.tolist()
-        if best is None or t[1] < best[1]:
+        if best is None or t[3] < best[3]:
             best = t
     peak = kernels.fp64_peak_tflops()
     flops = float(Nh) * n * (n + 1)
     QtQ = (Q.t() @ Q - torch.eye(Q.shape[1], dtype=torch.float64, device=dev)).abs().max().item()
     return {
-        "shape": [Nh, n], "num": 64, "sharding": f"snapshot columns over {world} GPUs, ring panels + all_reduce(G) + all_reduce(Q)",
-        "svd_time_ms": best[1], "gram_allreduce_ms": best[0],
+        "shape": [Nh, n], "num": 64,
+        "sharding": f"snapshot columns over {world} GPUs, " + ("every rank pulls the partners' columns from their memory (CUDA IPC over NVSwitch) into two panel buffers while the previous block is multiplied"
+                                                                if peer else "ring of send / receive panels") + " + all_reduce(G) + all_reduce(Y)",
+        "svd_time_ms": best[3], "gram_allreduce_ms": best[0], "eig_ms": best[1], "lift_refinement_ms": best[2],
+        "breakdown": "nested CUDA events of the same run (max over ranks per phase)", "peer_mapping_setup_ms_once": t_map,
         "gram_tflops_sym_half_aggregate": flops / best[0] * 1e-9,
         "gram_frac_of_fp64_peak_aggregate": flops / best[0] * 1e-9 / (peak * world),
-        "S_GBps_whole_orth": 8.0 * Nh * n / best[1] * 1e-6, "QtQ_minus_I_max": QtQ,
+        "S_GBps_whole_orth": 8.0 * Nh * n / best[3] * 1e-6, "QtQ_minus_I_max": QtQ,
         "energy_last": float(energy[-1]), "singular_values_head": [float(x) for x in s[:4]],
+        "same_input_check": same,
     }

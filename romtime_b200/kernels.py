@@ -95,8 +95,15 @@ def pod_gram(S, normalize=True):
     return G, cn
 
 
+def enable_peer_access(peer, device=None):
+    """rt_enable_peer_access: kernels of ``device`` (default: current) may read buffers living on device ``peer``."""
+    h = handle(device)
+    check(load_library().rt_enable_peer_access(h, int(peer)), h, "rt_enable_peer_access")
+
+
 def gram_cross(A, B):
-    """rt_gram_cross_f64: C = A^T B (na x nb) for A (Nh x na), B (Nh x nb)."""
+    """rt_gram_cross_f64: C = A^T B (na x nb) for A (Nh x na), B (Nh x nb).  The call runs on A's device; B may be peer
+    memory (a CUDA tensor of another device after enable_peer_access)."""
     Ad, Bd = to_device(A), to_device(B)
     Nh, na = Ad.shape
     Nh2, nb = Bd.shape
