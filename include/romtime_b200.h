@@ -276,6 +276,25 @@ int64_t rt_launch_count(const rt_handle* h);
 int rt_small_gram_eig_f64(rt_handle* h, const double* G_all, int64_t stride_g, const int* n_of, int64_t P,
                           int64_t nmax, double* w_all, double* W_all, int64_t stride_w, int* rank, int* info,
                           void* stream);
+/* The Gram matrices / lifts of a batch, queued by one call: d[p] (HOST array) holds the arguments of rt_pod_gram_f64 /
+ * rt_pod_lift_f64 for problem p (device pointers). */
+typedef struct {
+    const double* S;
+    int64_t Nh, n, stride_row, stride_col;
+    double* G;       /* n x n, leading dimension n */
+    double* colnorm; /* n */
+} rt_gram_desc;
+typedef struct {
+    const double* S;
+    int64_t Nh, n, stride_row, stride_col;
+    const double* Wr;
+    int64_t ldw, r;
+    double* Q;
+    int64_t q_stride_row, q_stride_col;
+} rt_lift_desc;
+int rt_pod_gram_batch_f64(rt_handle* h, const rt_gram_desc* d, int64_t P, int normalize, void* stream);
+int rt_pod_lift_batch_f64(rt_handle* h, const rt_lift_desc* d, int64_t P, void* stream);
+
 /* rt_small_refine_f64: the Hestenes refinement step for a batch: H_p = Y_p^T Y_p (c_p x c_p row-major, leading dimension
  * c_p, c_of[p] = c_p <= cmax <= 96) of lifted, nearly orthogonal graded columns -> all eigenpairs with small RELATIVE
  * errors (Cholesky + one-sided Jacobi).  Out: lam_all[p * cmax + k] descending, X_all + p * stride_x (c_p x c_p row-major,

@@ -62,6 +62,8 @@ SIGNATURES = {
     "rt_deflate_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "rt_pod_lift_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp]),
     "rt_small_gram_eig_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
+    "rt_pod_gram_batch_f64": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp]),
+    "rt_pod_lift_batch_f64": (c_int, [c_vp, c_vp, c_i64, c_vp]),
     "rt_small_refine_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "rt_deim_greedy_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "rt_project_vec_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp]),

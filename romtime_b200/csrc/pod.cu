@@ -127,6 +127,29 @@ extern "C" int rt_pod_lift_f64(rt_handle* h, const double* S, int64_t Nh, int64_
     return dg::launch(h, a, b, p, st);
 }
 
+// Batched forms for the tree-walk PODs: P small problems described by HOST arrays of descriptors, queued back to back on the
+// stream by ONE call (the per-call cost of the Python binding, not the kernels, dominates at 100 x 50 snapshot blocks).
+extern "C" int rt_pod_gram_batch_f64(rt_handle* h, const rt_gram_desc* d, int64_t P, int normalize, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, d && P >= 1);
+    for (int64_t p = 0; p < P; ++p) {
+        int rc = rt_pod_gram_f64(h, d[p].S, d[p].Nh, d[p].n, d[p].stride_row, d[p].stride_col, normalize, d[p].G, d[p].colnorm, stream);
+        if (rc) return rc;
+    }
+    return RT_OK;
+}
+
+extern "C" int rt_pod_lift_batch_f64(rt_handle* h, const rt_lift_desc* d, int64_t P, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, d && P >= 1);
+    for (int64_t p = 0; p < P; ++p) {
+        int rc = rt_pod_lift_f64(h, d[p].S, d[p].Nh, d[p].n, d[p].stride_row, d[p].stride_col, d[p].Wr, d[p].ldw, d[p].r, d[p].Q,
+                                 d[p].q_stride_row, d[p].q_stride_col, stream);
+        if (rc) return rc;
+    }
+    return RT_OK;
+}
+
 // Deflation step of the POD's second level (romtime_b200/rom/pod.py): with P = Q (Q^T S D^-1) already in `P`
 // (rt_gram_cross_f64 + rt_pod_lift_f64), P <- S D^-1 - P is what the delivered modes Q leave of the (column-normalised)
 // snapshots.  colnorm == NULL: D = I.  P is Nh x n row-major.

@@ -198,6 +198,38 @@ def sym_eig_jacobi(H):
 SMALL_NMAX, SMALL_RMAX = 256, 96  # limits of the batched small-POD kernels (include/romtime_b200.h)
 
 
+GRAM_DESC = np.dtype([("S", "u8"), ("Nh", "i8"), ("n", "i8"), ("srow", "i8"), ("scol", "i8"), ("G", "u8"), ("cn", "u8")])
+LIFT_DESC = np.dtype([("S", "u8"), ("Nh", "i8"), ("n", "i8"), ("srow", "i8"), ("scol", "i8"), ("W", "u8"), ("ldw", "i8"), ("r", "i8"),
+                      ("Q", "u8"), ("qrow", "i8"), ("qcol", "i8")])
+
+
+def pod_gram_batch(mats, G_all, cn_all, stride_g, stride_cn, normalize):
+    """rt_pod_gram_batch_f64: Gram matrix of every CUDA matrix in ``mats`` into slot j of G_all (leading dimension n_j) and
+    its column norms into slot j of cn_all -- one call, nothing synchronised."""
+    d = np.zeros(len(mats), dtype=GRAM_DESC)
+    for j, S in enumerate(mats):
+        d[j] = (S.data_ptr(), S.shape[0], S.shape[1], S.stride(0), S.stride(1), G_all.data_ptr() + 8 * j * stride_g,
+                cn_all.data_ptr() + 8 * j * stride_cn)
+    dev = G_all.device
+    h = handle(dev.index)
+    with torch.cuda.device(dev):
+        rc = load_library().rt_pod_gram_batch_f64(h, c_vp(d.ctypes.data), len(mats), int(bool(normalize)), stream_ptr())
+    check(rc, h, "rt_pod_gram_batch_f64")
+
+
+def pod_lift_batch(items):
+    """rt_pod_lift_batch_f64: Q_j = S_j @ W_j for every (S_j, W_j contiguous, Q_j) of CUDA tensors -- one call."""
+    d = np.zeros(len(items), dtype=LIFT_DESC)
+    for j, (S, W, Q) in enumerate(items):
+        d[j] = (S.data_ptr(), S.shape[0], S.shape[1], S.stride(0), S.stride(1), W.data_ptr(), W.stride(0), W.shape[1],
+                Q.data_ptr(), Q.stride(0), Q.stride(1))
+    dev = items[0][0].device
+    h = handle(dev.index)
+    with torch.cuda.device(dev):
+        rc = load_library().rt_pod_lift_batch_f64(h, c_vp(d.ctypes.data), len(items), stream_ptr())
+    check(rc, h, "rt_pod_lift_batch_f64")
+
+
 def small_gram_eig(G_all, n_of, nmax):
     """rt_small_gram_eig_f64 for a batch of Gram matrices packed in G_all (P x nmax*nmax).  Returns device tensors
     (w_all P x nmax, W_all P x nmax*nmax, rank P, info P); nothing is synchronised."""

@@ -209,34 +209,66 @@ def orth_device(S, num=None, tol=None, normalize=True, allreduce=None, deflate=T
     return Q, s, energy, VT, info
 
 
+_STAGING = [None]   # grow-only pinned staging buffer of the packed transfers (cudaHostAlloc costs more than the copy)
+
+
+def _pinned(count):
+    if _STAGING[0] is None or _STAGING[0].numel() < count:
+        _STAGING[0] = torch.empty(max(count, 1 << 20), dtype=torch.float64, pin_memory=True)
+    return _STAGING[0][:count]
+
+
+def _to_device_packed(mats):
+    """NumPy blocks -> CUDA tensors through ONE pinned staging buffer and ONE host-to-device copy (CUDA tensors pass through).
+    Every block keeps C order; block starts are 16-byte aligned so that TMA can address them."""
+    idx = [i for i, S in enumerate(mats) if not isinstance(S, torch.Tensor)]
+    out = [S if isinstance(S, torch.Tensor) else None for S in mats]
+    if not idx:
+        return [kernels.to_device(S) for S in out]
+    arrs = {i: np.asarray(mats[i], dtype=np.float64) for i in idx}
+    offs, total = {}, 0
+    for i in idx:
+        offs[i] = total
+        total += (arrs[i].size + 1) & ~1
+    if not torch.cuda.is_available():
+        kernels.to_device(arrs[idx[0]])   # raises: there is no CPU fallback
+    host = _pinned(max(total, 2))
+    hv = host.numpy()
+    for i in idx:
+        hv[offs[i]: offs[i] + arrs[i].size] = arrs[i].reshape(-1)       # C-order copy whatever the source order
+    dev = host.to("cuda", non_blocking=True)
+    torch.cuda.current_stream().synchronize()   # the staging buffer is reused by the next batch
+    for i in idx:
+        out[i] = dev[offs[i]: offs[i] + arrs[i].size].view(arrs[i].shape)
+    return [kernels.to_device(S) for S in out]
+
+
 def orth_device_batch(mats, num=None, tol=None, normalize=True):
     """The same POD for a BATCH of small snapshot matrices (the per-parameter time-PODs of a tree walk), with the host
-    out of the inner loop: the Gram matrices and lifts of all problems are queued back to back, the eigen-work of the
-    whole batch is two launches (rt_small_gram_eig_f64, rt_small_refine_f64: one CTA per problem), and the host reads
-    spectra twice per BATCH instead of ~5 times per matrix.  Same algorithm and decisions as ``orth_device`` (Gram ->
-    eigensolve -> lift of the wanted + guard modes -> Hestenes refinement); any problem outside the fast path's limits
-    (more than 256 snapshots, numerical rank or candidate count above 96, a truncation rule that reaches below the
-    first Gram matrix's floor, a refinement that needs a second pass) goes through ``orth_device`` unchanged.
+    out of the inner loop: one packed host-to-device copy, the Gram matrices and lifts of all problems queued by one call
+    each (rt_pod_gram_batch_f64 / rt_pod_lift_batch_f64), the eigen-work of the whole batch in two launches
+    (rt_small_gram_eig_f64, rt_small_refine_f64: one CTA per problem), and the host reads spectra twice per BATCH instead
+    of ~5 times per matrix.  Same algorithm and decisions as ``orth_device`` (Gram -> eigensolve -> lift of the wanted +
+    guard modes -> Hestenes refinement); any problem outside the fast path's limits (more than 256 snapshots, numerical
+    rank or candidate count above 96, a truncation rule that reaches below the first Gram matrix's floor, a refinement
+    that needs a second pass) goes through ``orth_device`` unchanged.
     Returns a list of (Q cuda Nh x r, s numpy, energy numpy)."""
     P = len(mats)
     out = [None] * P
-    Sd = [kernels.to_device(S) for S in mats]
+    Sd = _to_device_packed(list(mats))
     default_rule = not tol and not num
     fast = [i for i in range(P) if Sd[i].dim() == 2 and 1 <= Sd[i].shape[1] <= kernels.SMALL_NMAX and Sd[i].shape[0] >= 1]
     if len(fast) >= 2:
         dev = Sd[fast[0]].device
+        f64 = torch.float64
         nmax = max(Sd[i].shape[1] for i in fast)
-        G_all = torch.zeros((len(fast), nmax * nmax), dtype=torch.float64, device=dev)
-        cns = {}
-        for j, i in enumerate(fast):
-            G, cn = kernels.pod_gram(Sd[i], normalize=bool(normalize))
-            n = Sd[i].shape[1]
-            G_all[j, : n * n] = G.reshape(-1)
-            cns[i] = cn
+        G_all = torch.zeros((len(fast), nmax * nmax), dtype=f64, device=dev)
+        cn_all = torch.empty((len(fast), nmax), dtype=f64, device=dev)
+        kernels.pod_gram_batch([Sd[i] for i in fast], G_all, cn_all, nmax * nmax, nmax, normalize)
         n_of = torch.tensor([Sd[i].shape[1] for i in fast], dtype=torch.int32).to(dev)
         w_all, W_all, rank_d, info_d = kernels.small_gram_eig(G_all, n_of, nmax)
         w_h, rank_h, info_h = w_all.cpu().numpy(), rank_d.cpu().numpy(), info_d.cpu().numpy()   # host read 1 of 2
-        plan = []  # (slot, problem, s_tail, rank, want, c, Y)
+        plan = []  # [slot, problem, s_tail, rank, want, c]
         for j, i in enumerate(fast):
             Nh, n = Sd[i].shape
             k = min(Nh, n)
@@ -252,21 +284,32 @@ def orth_device_batch(mats, num=None, tol=None, normalize=True):
             c = _guard_width(s_tail, want, rank)
             if c > kernels.SMALL_RMAX:
                 continue
-            W = W_all[j, : n * n].reshape(n, n)
-            Wc = W[:, :c].contiguous()
-            Wl = (Wc / cns[i][:, None]).contiguous() if normalize else Wc
-            Y = kernels.pod_lift(Sd[i], Wl, order="F")
-            plan.append([j, i, s_tail, rank, want, c, Y])
+            plan.append([j, i, s_tail, rank, want, c])
         if plan:
+            # lifts Y = S D^-1 W_c of the whole batch: the scaled right vectors packed in one buffer, one call
             cmax = max(pl[5] for pl in plan)
-            H_all = torch.zeros((len(plan), cmax * cmax), dtype=torch.float64, device=dev)
-            for jj, pl in enumerate(plan):
-                H = kernels.pod_gram(pl[6], normalize=False)[0]
-                H_all[jj, : pl[5] * pl[5]] = H.reshape(-1)
+            Wl_all = torch.empty((len(plan), nmax * cmax), dtype=f64, device=dev)
+            Ys, items = [], []
+            for jj, (j, i, s_tail, rank, want, c) in enumerate(plan):
+                Nh, n = Sd[i].shape
+                W = W_all[j, : n * n].view(n, n)
+                Wl = Wl_all[jj, : n * c].view(n, c)
+                if normalize:
+                    torch.div(W[:, :c], cn_all[j, :n, None], out=Wl)
+                else:
+                    Wl.copy_(W[:, :c])
+                Y = torch.empty((c, Nh), dtype=f64, device=dev).t()         # F-ordered like pod_lift(order="F")
+                Ys.append(Y)
+                items.append((Sd[i], Wl, Y))
+            kernels.pod_lift_batch(items)
+            H_all = torch.zeros((len(plan), cmax * cmax), dtype=f64, device=dev)
+            hn_all = torch.empty((len(plan), cmax), dtype=f64, device=dev)
+            kernels.pod_gram_batch(Ys, H_all, hn_all, cmax * cmax, cmax, False)
             c_of = torch.tensor([pl[5] for pl in plan], dtype=torch.int32).to(dev)
             lam_all, X_all, defect_d, info2_d = kernels.small_refine(H_all, c_of, cmax)
             lam_h, defect_h, info2_h = lam_all.cpu().numpy(), defect_d.cpu().numpy(), info2_d.cpu().numpy()   # host read 2 of 2
-            for jj, (j, i, s_tail, rank, want, c, Y) in enumerate(plan):
+            finals = []
+            for jj, (j, i, s_tail, rank, want, c) in enumerate(plan):
                 if info2_h[jj] != 0 or c * defect_h[jj] > 0.1:
                     continue   # needs a second rotation pass: general path
                 Nh, n = Sd[i].shape
@@ -280,11 +323,26 @@ def orth_device_batch(mats, num=None, tol=None, normalize=True):
                 if rank < k and (r_total > want or (default_rule and floor_abs > DROP_TOLERANCE)):
                     continue   # the rule reaches below this Gram matrix's floor: deflated levels of the general path
                 keep = min(r_total, want)
+                if keep == 0:
+                    out[i] = (torch.empty((0, Nh), dtype=f64, device=dev).t(), s, energy)
+                    continue
                 inv = np.divide(1.0, sc[:keep], out=np.zeros(keep), where=sc[:keep] > 0)
-                X = X_all[jj, : c * c].reshape(c, c)
-                Xr = (X[:, :keep] * torch.as_tensor(inv, device=dev)).contiguous()
-                Q = kernels.pod_lift(Y, Xr, order="F")
-                out[i] = (Q, s, energy)
+                finals.append((jj, i, keep, inv, s, energy))
+            if finals:
+                inv_all = torch.zeros((len(finals), cmax), dtype=f64)
+                for f, (jj, i, keep, inv, s, energy) in enumerate(finals):
+                    inv_all[f, :keep] = torch.from_numpy(inv)
+                inv_all = inv_all.to(dev)
+                Xr_all = torch.empty((len(finals), cmax * cmax), dtype=f64, device=dev)
+                items = []
+                for f, (jj, i, keep, inv, s, energy) in enumerate(finals):
+                    c = plan[jj][5]
+                    Xr = Xr_all[f, : c * keep].view(c, keep)
+                    torch.mul(X_all[jj, : c * c].view(c, c)[:, :keep], inv_all[f, None, :keep], out=Xr)
+                    Q = torch.empty((keep, Sd[i].shape[0]), dtype=f64, device=dev).t()
+                    items.append((Ys[jj], Xr, Q))
+                    out[i] = (Q, s, energy)
+                kernels.pod_lift_batch(items)
     for i in range(P):
         if out[i] is None:
             Q, s, energy, _, _ = orth_device(Sd[i], num=num, tol=tol, normalize=normalize)
@@ -299,7 +357,23 @@ def orth_batch(snapshots_list, num=None, tol=None, normalize=True):
         if isinstance(S, list):
             raise ValueError("You should use an array, not a list.")
     res = orth_device_batch(list(snapshots_list), num=num, tol=tol, normalize=(normalize == True))  # noqa: E712
-    return [(Q.cpu().numpy(), s, energy) for Q, s, energy in res]
+    if not res:
+        return []
+    # ONE packed device-to-host copy of all bases (F-ordered blocks, like LAPACK's U)
+    sizes = [Q.shape[0] * Q.shape[1] for Q, _, _ in res]
+    dev = res[0][0].device
+    pack = torch.empty(max(sum(sizes), 1), dtype=torch.float64, device=dev)
+    off = 0
+    for (Q, _, _), sz in zip(res, sizes):
+        if sz:
+            pack[off: off + sz].view(Q.shape[1], Q.shape[0]).copy_(Q.t())
+        off += sz
+    host = pack.cpu().numpy()
+    out, off = [], 0
+    for (Q, s, energy), sz in zip(res, sizes):
+        out.append((host[off: off + sz].reshape(Q.shape[1], Q.shape[0]).T, s, energy))
+        off += sz
+    return out
 
 
 def orth(snapshots, num=None, tol=None, normalize=True, return_VT=False):
