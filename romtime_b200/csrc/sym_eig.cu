@@ -36,6 +36,10 @@ constexpr int BS = 32;        // block size
 constexpr int TS = 2 * BS;    // tile (sub-problem) size
 constexpr int LDS_ = TS + 4;  // shared-memory leading dimension (68 == 4 mod 16: conflict-free DMMA fragments)
 constexpr double kEps = 2.220446049250313e-16;
+// A sweep whose rotations all had |a_pq| <= kBigRotation * sqrt(a_pp a_qq) leaves off-diagonal entries of the order of the
+// SQUARE of that (cyclic Jacobi converges quadratically): below the rotation threshold, so the sweep that would only verify
+// "no rotation left" is not run.  The sub-problem kernel counts those rotations in the upper half of the sweep counter.
+constexpr double kBigRotation = 1e-10;
 
 __device__ __forceinline__ void rr_pair(int round, int k, int nb, int& I, int& J) {
     // circle method on nb (even) players: every unordered pair meets exactly once in nb-1 rounds
@@ -65,109 +69,139 @@ __global__ void k_maxdiag(const double* __restrict__ A, int64_t n, int64_t lda, 
 }
 
 // ---- (1) 64 x 64 sub-problem: cyclic two-sided Jacobi with parallel ordering, in shared memory ----
-__global__ void __launch_bounds__(256) k_jacobi_sub(double* __restrict__ A, int64_t lda, int round, int nb,
-                                                    double* __restrict__ Wbuf, unsigned long long* rot_count,
-                                                    const double* __restrict__ maxdiag, double floor_rel, int max_inner) {
+// 1 / x to ~1 ulp: MUFU.RCP64H seed and one third-order step (x > 0, normal)
+__device__ __forceinline__ double fast_rcp(double x) {
+    double x0;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x0) : "d"(x));
+    const double e = fma(-x, x0, 1.0);
+    return fma(x0, fma(e, e, e), x0);
+}
+
+// One plane rotation: (c, s) annihilating a_pq; rot = false (c = 1, s = 0) when
+// |a_pq| <= max(eps sqrt(|a_pp a_qq|), floor_rel * max|diag|); big = the entry was above kBigRotation * sqrt(|a_pp a_qq|).
+__device__ __forceinline__ void jacobi_rotation(double apq_raw, double app_raw, double aqq_raw, double inv_md, double floor_rel,
+                                                double& c, double& s, bool& rot, bool& big) {
+    // entries relative to the largest diagonal entry: the squares below neither overflow nor underflow
+    const double apq = apq_raw * inv_md, app = app_raw * inv_md, aqq = aqq_raw * inv_md;
+    c = 1.0; s = 0.0;
+    // |a_pq| > eps sqrt(|a_pp a_qq|), compared squared (no square root on the chain)
+    const double mag2 = apq * apq, dd = fabs(app * aqq);
+    rot = mag2 > (kEps * kEps) * dd && fabs(apq) > floor_rel;
+    big = rot && mag2 > (kBigRotation * kBigRotation) * dd;
+    if (rot) {
+        // t = sign(tau) / (|tau| + sqrt(1 + tau^2)), tau = (a_qq - a_pp) / (2 a_pq), with the first division folded away:
+        // t = sign(d) o / (|d| + sqrt(d^2 + o^2)),  d = a_qq - a_pp,  o = 2 a_pq
+        const double d = aqq - app, o = 2.0 * apq;
+        const double x = fma(d, d, o * o);
+        const double hyp = x * rsqrt(x);
+        const double t = copysign(1.0, d) * o * fast_rcp(fabs(d) + hyp);
+        c = rsqrt(fma(t, t, 1.0));
+        s = t * c;
+    }
+}
+
+// The two-sided update of one 2 x 2 block (rows = pair (p, q) with rotation (c, sn), columns = pair (p2, q2) with (c2, s2)):
+// column rotation, then row rotation, in registers; the diagonal block writes the annihilated entry as an exact zero.
+__device__ __forceinline__ void rotate_block(double c, double sn, double c2, double s2, bool diagonal,
+                                             double& xpp, double& xpq, double& xqp, double& xqq) {
+    if (s2 != 0.0) {  // columns (p2, q2):  [x y] <- [c2 x - s2 y, s2 x + c2 y]
+        const double t0 = c2 * xpp - s2 * xpq, t1 = s2 * xpp + c2 * xpq;
+        const double t2 = c2 * xqp - s2 * xqq, t3 = s2 * xqp + c2 * xqq;
+        xpp = t0; xpq = t1; xqp = t2; xqq = t3;
+    }
+    if (sn != 0.0) {  // rows (p, q)
+        const double t0 = c * xpp - sn * xqp, t2 = sn * xpp + c * xqp;
+        const double t1 = c * xpq - sn * xqq, t3 = sn * xpq + c * xqq;
+        xpp = t0; xpq = t1; xqp = t2; xqq = t3;
+        if (diagonal) { xpq = 0.0; xqp = 0.0; }
+    }
+}
+
+// One step = 32 disjoint rotations (parallel ordering): warp 0 computes them, then 512 threads apply A <- J^T A J block
+// by block while 256 threads accumulate W <- W J (the two passes side by side: the shared-memory latency of one hides
+// under the other).  Measured on B200 (clock64 around the phases, 63 steps of a full sub-problem): the rotation chain
+// costs 500 (nothing rotates) to 950 cycles per step, the update 300 to 1000, both through shared memory (one step moves
+// both matrices: 128 KB at 128 B / clock).  Tried and not kept: the rotations of the NEXT step computed by a 25th warp
+// from a second matrix buffer while the update runs (one barrier per step, but every block must then be copied even
+// when nothing rotates: late sweeps slow down as much as early ones gain), and W accumulated by a second CTA from a
+// global log of the rotations (the fence that publishes a step costs what the shorter update saves).
+constexpr int kSubThreads = 768;
+
+__global__ void __launch_bounds__(kSubThreads) k_jacobi_sub(double* __restrict__ A, int64_t lda, int round, int nb,
+                                                            double* __restrict__ Wbuf, unsigned long long* rot_count,
+                                                            const double* __restrict__ maxdiag, double floor_rel) {
     constexpr int LD = TS + 1;
     extern __shared__ __align__(16) double sub_sm[];
     double* a = sub_sm;
     double* w = sub_sm + TS * LD;
     __shared__ double cs_c[BS], cs_s[BS];
     __shared__ int pp[BS], qq[BS];
-    __shared__ int rotated;
-    __shared__ unsigned long long total;
 
     const int tid = threadIdx.x;
     int I, J;
     rr_pair(round, blockIdx.x, nb, I, J);
-    for (int e = tid; e < TS * TS; e += 256) {
+    for (int e = tid; e < TS * TS; e += kSubThreads) {
         const int r = e / TS, c = e % TS;
         a[r * LD + c] = A[(int64_t)tile_index(I, J, r) * lda + tile_index(I, J, c)];
         w[r * LD + c] = (r == c) ? 1.0 : 0.0;
     }
-    if (tid == 0) total = 0;
     __syncthreads();
     // absolute floor (relative to the largest diagonal entry) below which entries are not rotated:
     // a safeguard only -- M = L^T L from the pivoted Cholesky factor is a graded PSD matrix on which the
     // relative test is stable, so the caller passes a tiny value
-    const double floor_abs = floor_rel * maxdiag[0];
+    const double md = maxdiag[0];
+    const double inv_md = md > 0.0 ? 1.0 / md : 1.0;
 
-    // One step = 32 disjoint rotations (parallel ordering).  The two-sided update A <- J^T A J is applied per 2 x 2 block
-    // (rows = pair r, columns = pair r2): column rotation of pair r2, then row rotation of pair r, in registers -- the
-    // same operations per element as a column pass followed by a row pass, with one barrier instead of two.  The block
-    // (r, r) writes the annihilated entry as an exact zero.
-    const int ur = tid >> 3, uc = tid & 7;   // A blocks (ur, uc + 8k), k < 4
-    const int wr = tid & 31, wi = tid >> 5;  // W: pair wr, rows wi + 8k, k < 8
-    for (int sweep = 0; sweep < max_inner; ++sweep) {
-        if (tid == 0) rotated = 0;
-        __syncthreads();
-        for (int step = 0; step < TS - 1; ++step) {
-            if (tid < BS) {
-                int p, q;
-                rr_pair(step, tid, TS, p, q);
-                const double apq = a[p * LD + q], app = a[p * LD + p], aqq = a[q * LD + q];
-                double c = 1.0, s = 0.0;
-                const double mag = fabs(apq);
-                if (mag > kEps * sqrt(fabs(app) * fabs(aqq)) && mag > floor_abs) {
-                    const double tau = (aqq - app) / (2.0 * apq);
-                    double t;
-                    if (fabs(tau) > 1e150) t = 0.5 / tau;
-                    else t = copysign(1.0, tau) / (fabs(tau) + sqrt(1.0 + tau * tau));
-                    c = rsqrt(1.0 + t * t);
-                    s = t * c;
-                    atomicAdd(&rotated, 1);
-                }
-                cs_c[tid] = c; cs_s[tid] = s; pp[tid] = p; qq[tid] = q;
-            }
-            __syncthreads();
-            {
-                const double c = cs_c[ur], sn = cs_s[ur];
-                const int p = pp[ur], q = qq[ur];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int r2 = uc + 8 * k;
-                    const double c2 = cs_c[r2], s2 = cs_s[r2];
-                    if (sn == 0.0 && s2 == 0.0) continue;
-                    const int p2 = pp[r2], q2 = qq[r2];
-                    double xpp = a[p * LD + p2], xpq = a[p * LD + q2], xqp = a[q * LD + p2], xqq = a[q * LD + q2];
-                    if (s2 != 0.0) {  // columns (p2, q2):  [x y] <- [c2 x - s2 y, s2 x + c2 y]
-                        const double t0 = c2 * xpp - s2 * xpq, t1 = s2 * xpp + c2 * xpq;
-                        const double t2 = c2 * xqp - s2 * xqq, t3 = s2 * xqp + c2 * xqq;
-                        xpp = t0; xpq = t1; xqp = t2; xqq = t3;
-                    }
-                    if (sn != 0.0) {  // rows (p, q)
-                        const double t0 = c * xpp - sn * xqp, t2 = sn * xpp + c * xqp;
-                        const double t1 = c * xpq - sn * xqq, t3 = sn * xpq + c * xqq;
-                        xpp = t0; xpq = t1; xqp = t2; xqq = t3;
-                        if (r2 == ur) { xpq = 0.0; xqp = 0.0; }
-                    }
-                    a[p * LD + p2] = xpp; a[p * LD + q2] = xpq; a[q * LD + p2] = xqp; a[q * LD + q2] = xqq;
-                }
-                const double c2 = cs_c[wr], s2 = cs_s[wr];
-                if (s2 != 0.0) {
-                    const int p2 = pp[wr], q2 = qq[wr];
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const int i = wi + 8 * k;
-                        const double u = w[i * LD + p2], v = w[i * LD + q2];
-                        w[i * LD + p2] = c2 * u - s2 * v;
-                        w[i * LD + q2] = s2 * u + c2 * v;
-                    }
-                }
-            }
-            __syncthreads();
+    const int ur = (tid >> 4) & 31, uc = tid & 15;   // A: block row ur, block columns uc + 16k, k < 2
+    const int wr = tid & 31, wi = (tid >> 5) & 7;    // W: pair wr, rows wi + 8k, k < 8
+    int rotated = 0, rotated_big = 0;                // thread 0
+    for (int step = 0; step < TS - 1; ++step) {
+        if (tid < BS) {
+            int p, q;
+            rr_pair(step, tid, TS, p, q);
+            double c, s;
+            bool rot, big;
+            jacobi_rotation(a[p * LD + q], a[p * LD + p], a[q * LD + q], inv_md, floor_rel, c, s, rot, big);
+            rotated += __popc(__ballot_sync(0xffffffffu, rot));
+            rotated_big += __popc(__ballot_sync(0xffffffffu, big));
+            cs_c[tid] = c; cs_s[tid] = s; pp[tid] = p; qq[tid] = q;
         }
-        if (tid == 0) total += (unsigned long long)rotated;
-        const int r = rotated;
         __syncthreads();
-        if (r == 0) break;
+        if (tid < 512) {
+            const double c = cs_c[ur], sn = cs_s[ur];
+            const int p = pp[ur], q = qq[ur];
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int r2 = uc + 16 * k;
+                const double c2 = cs_c[r2], s2 = cs_s[r2];
+                if (sn == 0.0 && s2 == 0.0) continue;
+                const int p2 = pp[r2], q2 = qq[r2];
+                double xpp = a[p * LD + p2], xpq = a[p * LD + q2], xqp = a[q * LD + p2], xqq = a[q * LD + q2];
+                rotate_block(c, sn, c2, s2, r2 == ur, xpp, xpq, xqp, xqq);
+                a[p * LD + p2] = xpp; a[p * LD + q2] = xpq; a[q * LD + p2] = xqp; a[q * LD + q2] = xqq;
+            }
+        } else {
+            const double c2 = cs_c[wr], s2 = cs_s[wr];
+            if (s2 != 0.0) {
+                const int p2 = pp[wr], q2 = qq[wr];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int i = wi + 8 * k;
+                    const double u = w[i * LD + p2], v = w[i * LD + q2];
+                    w[i * LD + p2] = c2 * u - s2 * v;
+                    w[i * LD + q2] = s2 * u + c2 * v;
+                }
+            }
+        }
+        __syncthreads();
     }
-    for (int e = tid; e < TS * TS; e += 256) {
+    for (int e = tid; e < TS * TS; e += kSubThreads) {
         const int r = e / TS, c = e % TS;
         A[(int64_t)tile_index(I, J, r) * lda + tile_index(I, J, c)] = a[r * LD + c];
         Wbuf[(size_t)blockIdx.x * TS * TS + e] = w[r * LD + c];
     }
-    if (tid == 0 && total) atomicAdd(rot_count, total);
+    if (tid == 0 && rotated)
+        atomicAdd(rot_count, (unsigned long long)rotated + ((unsigned long long)rotated_big << 32));
 }
 
 // ---- (2) tile updates with DMMA:  A_kl <- W_k^T A_kl W_l  (k < l),  V_rl <- V_rl W_l ----
@@ -501,13 +535,12 @@ static int jacobi_eig(rt_handle* h, const double* Ain, int64_t n, int64_t lda_in
     const int rounds = nb - 1;
     const int max_sweeps = 60;
     // one inner sweep per sub-problem and round: the outer iteration converges in the same number of sweeps (7-9 on the
-    // POD Gram matrices) as with fully converged sub-problems, each 3-5x cheaper (RT_EIG_INNER overrides, for experiments)
-    const int max_inner = getenv("RT_EIG_INNER") ? atoi(getenv("RT_EIG_INNER")) : 1;
+    // POD Gram matrices) as with fully converged sub-problems, each 3-5x cheaper
     int sweeps_used = -1;
     for (int sweep = 0; sweep < max_sweeps; ++sweep) {
         RT_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st));
         for (int round = 0; round < rounds; ++round) {
-            k_jacobi_sub<<<P, 256, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag, floor_rel, max_inner);
+            k_jacobi_sub<<<P, kSubThreads, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag, floor_rel);
             RT_LAUNCH_CHECK(h);
             k_jacobi_apply<<<nA + nV, 256, apply_smem, st>>>(A, V, npad, round, nb, Wbuf, nA);
             RT_LAUNCH_CHECK(h);
@@ -515,8 +548,10 @@ static int jacobi_eig(rt_handle* h, const double* Ain, int64_t n, int64_t lda_in
         unsigned long long rot = 0;
         RT_CUDA(h, cudaMemcpyAsync(&rot, counter, sizeof(rot), cudaMemcpyDeviceToHost, st));
         RT_CUDA(h, cudaStreamSynchronize(st));
-        if (getenv("RT_EIG_DEBUG")) fprintf(stderr, "[rt_sym_eig] n=%lld sweep %d rotations %llu\n", (long long)n, sweep, rot);
-        if (rot == 0) { sweeps_used = sweep + 1; break; }
+        if (getenv("RT_EIG_DEBUG"))
+            fprintf(stderr, "[rt_sym_eig] n=%lld sweep %d rotations %llu (above %.0e: %llu)\n", (long long)n, sweep,
+                    rot & 0xffffffffull, kBigRotation, rot >> 32);
+        if ((rot >> 32) == 0) { sweeps_used = sweep + 1; break; }
     }
     k_rank<<<(unsigned)ceil_div64(n, 128), 128, 0, st>>>(A, n, npad, rank, w);
     RT_LAUNCH_CHECK(h);

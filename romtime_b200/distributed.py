@@ -210,14 +210,16 @@ class PeerPanels:
         return self.key == (S_local.data_ptr(), tuple(S_local.shape), tuple(S_local.stride()))
 
 
-def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=False, panels=None):
+def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=False, panels=None, trace=None):
     """Same result as ``gram_column_sharded`` without a ring: rank g PULLS the columns of partner (g + h) % P straight from
     the owner's memory (CUDA IPC mapping, NVSwitch: full bandwidth between any pair) into one of two local panel buffers on
     a copy stream while block h - 1 is multiplied -- one transfer of each panel, no send / receive pairing, no transposing
     staging copy (the panel keeps the owner's layout), hop 1 hidden behind the diagonal block.
     ``direct=True``: no copy at all, the GEMM's TMA reads the B tiles from peer memory while the DMMAs run.  Measured
     slower: a peer tile is not cached in the LOCAL L2, so every tile row of the block re-reads the panel over NVLink
-    (4 x 4.1 GB per hop at 8 GPUs, 346 ms against 279 ms for the ring at 2 GPUs); kept for the record and for small blocks."""
+    (4 x 4.1 GB per hop at 8 GPUs, 346 ms against 279 ms for the ring at 2 GPUs); kept for the record and for small blocks.
+    ``trace`` (a dict, pull variant): filled with this rank's timeline in ms from the start -- when each panel copy began and
+    ended on the copy stream, when each block ended on the main stream, when the all-reduce ended."""
     ops = block_ops or DeviceBlockOps()
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
@@ -243,6 +245,13 @@ def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=Fals
         wmax = max(b - a for a, b in shards)
         bufs = [torch.empty((Nh, wmax), dtype=S_local.dtype, device=dev) for _ in range(min(2, hops))]
         ready, free = [None] * (hops + 1), [None] * len(bufs)
+        timed = trace is not None
+        began, block_end = [None] * (hops + 1), [None] * (hops + 1)
+
+        def mark(stream):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            return e
 
         def pull(h):
             src = srcs[h - 1]
@@ -251,13 +260,19 @@ def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=Fals
             with torch.cuda.stream(side):
                 if free[slot] is not None:
                     side.wait_event(free[slot])      # the block that used this buffer is done
+                if timed:
+                    began[h] = mark(side)
                 bufs[slot][:, :w].copy_(peers[src], non_blocking=True)
-                ready[h] = torch.cuda.Event()
+                ready[h] = torch.cuda.Event(enable_timing=timed)
                 ready[h].record(side)
 
+        if timed:
+            t_start = mark(main)
         side.wait_stream(main)
         pull(1)
         G[lo:hi, lo:hi] = ops.gram(S_local)
+        if timed:
+            block_end[0] = mark(main)
         for h, src in enumerate(srcs, start=1):
             if h + 1 <= hops and len(bufs) > 1:
                 pull(h + 1)
@@ -265,11 +280,19 @@ def gram_column_sharded_peer(S_local, n, block_ops=None, group=None, direct=Fals
             slot = (h - 1) % len(bufs)
             w = shards[src][1] - shards[src][0]
             _cross_block(ops, G, S_local, bufs[slot][:, :w], rank, src, shards, world % 2 == 0 and h == hops)
-            free[slot] = torch.cuda.Event()
+            free[slot] = torch.cuda.Event(enable_timing=timed)
             free[slot].record(main)
+            block_end[h] = free[slot]
             if h + 1 <= hops and len(bufs) == 1:
                 pull(h + 1)
     dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
+    if trace is not None and not direct:
+        t_end = mark(main)
+        torch.cuda.synchronize(dev)
+        trace["block_end_ms"] = [round(t_start.elapsed_time(e), 3) for e in block_end]
+        trace["copy_begin_ms"] = [round(t_start.elapsed_time(e), 3) for e in began[1:]]
+        trace["copy_end_ms"] = [round(t_start.elapsed_time(e), 3) for e in ready[1:]]
+        trace["allreduce_end_ms"] = round(t_start.elapsed_time(t_end), 3)
     # the partners read this rank's columns until THEIR pulls are done: the all-reduce orders that on the device (a rank
     # joins it only after its own blocks); the IPC mappings are closed once this rank's work has drained as well
     main.synchronize()

@@ -1,30 +1,40 @@
-"""Eigensolver timing on the Gram matrices of the two named POD shapes (rows reduced: the spectrum is what matters).
-C3-like: n = 4096, rank 256 graded + 1e-13 noise, normalised;  C4-like: n = 2048 matrix-snapshot family, not normalised."""
-import os, sys
+"""Eigensolve of the C3 Gram matrix alone (n = 4096, rank ~258): CUDA-event time of rt_sym_eig_f64 and of the refinement's
+small Jacobi, so the replicated part of the multi-GPU POD can be profiled without the 1M-row Gram.
+
+    python tools/time_eig.py [rows] [n]
+"""
+import os
+import sys
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from romtime_b200 import kernels, synthetic
 
-dev = torch.device("cuda")
-g = torch.Generator(device=dev).manual_seed(1003)
-k, Nh, n = 256, 60000, 4096
-sig = torch.pow(10.0, -torch.arange(k, dtype=torch.float64, device=dev) / 32.0)
-S3 = (torch.randn((Nh, k), dtype=torch.float64, device=dev, generator=g) * sig) @ torch.randn((k, n), dtype=torch.float64, device=dev, generator=g)
-S3 += 1e-13 * torch.randn((Nh, n), dtype=torch.float64, device=dev, generator=g)
-S4 = synthetic.mdeim_snapshots_device(60000, 2048, seed=1004)
-for name, S, norm in (("C3-like n=4096", S3, True), ("C4-like n=2048", S4, False)):
-    G, cn = kernels.pod_gram(S, normalize=norm)
-    G0 = G.clone()
-    kernels.sym_eig(G.clone())
-    best = 1e9
-    for _ in range(3):
-        Gc = G0.clone()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); w, W, sweeps = kernels.sym_eig(Gc); e1.record(); torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    r = int((w > 0).sum())
-    res = (G0 @ W[:, :r] - W[:, :r] * w[:r]).abs().max().item() / w[0].item()
-    orth = (W[:, :r].t() @ W[:, :r] - torch.eye(r, dtype=torch.float64, device=dev)).abs().max().item()
-    wt = torch.linalg.eigvalsh(G0).flip(0)
-    rel = ((w[:64] - wt[:64]).abs() / wt[:64]).max().item()
-    print(f"{name}: eig {best:.2f} ms, sweeps {sweeps}, rank {r}, residual {res:.2e}, orth {orth:.2e}, lambda[:64] rel vs eigvalsh {rel:.2e}")
+from romtime_b200 import kernels
+from romtime_b200.distributed import _bench_snapshots
+
+rows = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+dev = torch.device("cuda:0")
+S = _bench_snapshots(rows, n, 0, n, dev, noise_seed=None)
+G, cn = kernels.pod_gram(S, normalize=True)
+reps = 1 if os.environ.get("PROF_NO_WARMUP") == "1" else 4
+for it in range(reps):
+    Gc = G.clone()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    w, W, sweeps = kernels.sym_eig(Gc)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"sym_eig n={n}: {e0.elapsed_time(e1):.3f} ms, sweeps {sweeps}, rank {int((w > 0).sum())}")
+c = 72
+Y = kernels.pod_lift(S, (W[:, :c] / cn[:, None]).contiguous(), order="F")
+H = kernels.pod_gram(Y, normalize=False)[0]
+for it in range(reps):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    lam, X, _, defect = kernels.sym_eig_jacobi(H)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"sym_eig_jacobi c={c}: {e0.elapsed_time(e1):.3f} ms, defect {defect:.2e}")
