@@ -60,3 +60,17 @@ def place():
 
 timed("placing a block and its transpose in G", place)
 timed("torch.zeros G", lambda: torch.zeros((8 * w, 8 * w), dtype=torch.float64, device=dev))
+
+# ---- the lift / refinement phase of the 8-GPU POD on this rank's shapes (everything but the two all-reduces)
+c, r = 72, 64
+Wl = torch.randn((w, c), dtype=torch.float64, device=dev, generator=g)
+Y = kernels.pod_lift(A, Wl, order="C")
+X = torch.linalg.qr(torch.randn((c, c), dtype=torch.float64, device=dev, generator=g))[0]
+Xr = X[:, :r].contiguous()
+H = kernels.pod_gram(Y, normalize=False)[0]
+timed(f"lift  S_g ({rows} x {w}) W ({w} x {c}), C-order", lambda: kernels.pod_lift(A, Wl, order="C"))
+timed(f"H = Y^T Y ({rows} x {c})", lambda: kernels.pod_gram(Y, normalize=False))
+timed(f"Jacobi on H ({c} x {c}) incl. host syncs", lambda: kernels.sym_eig_jacobi(H))
+timed(f"Q = Y X_r ({rows} x {c} x {r}), F-order", lambda: kernels.pod_lift(Y, Xr, order="F"))
+Wc = torch.randn((8 * w, c), dtype=torch.float64, device=dev, generator=g)
+timed(f"VT = (W_c X)^T ({8 * w} x {c} x {r})", lambda: kernels.pod_lift(Wc, Xr, order="C"))
