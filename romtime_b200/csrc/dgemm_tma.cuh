@@ -120,8 +120,8 @@ __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& tm, 
     }
 }
 
-template <int MI_>
-__device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI][2], double* C, int64_t ldc_m,
+template <int MI_, int NI_>
+__device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI_][2], double* C, int64_t ldc_m,
                                           int64_t ldc_n, int64_t M, int64_t N, int64_t m_base,
                                           int64_t n_base, int g, int tig, double alpha) {
     const bool vec = (ldc_n == 1) && ((ldc_m & 1) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
@@ -130,7 +130,7 @@ __device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI][2], doubl
         const int64_t m = m_base + 8 * i + g;
         if (m >= M) continue;
 #pragma unroll
-        for (int j = 0; j < NI; ++j) {
+        for (int j = 0; j < NI_; ++j) {
             const int64_t n = n_base + 8 * j + 2 * tig;
             if (n >= N) continue;
             double* dst = C + m * ldc_m + n * ldc_n;
@@ -145,9 +145,11 @@ __device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI][2], doubl
     }
 }
 
-// NARROW (N <= 64, one column of tiles): the right half of the 128 x 128 tile would be all padding, so the eight consumer
-// warps split the rows instead (16 rows x 64 columns each) and half of the DMMAs disappear (the POD lift S W_r, r <= 64).
-template <int AMAJOR, int BMAJOR, bool NARROW>
+// NT > 0 (N <= 8 NT <= 96, one column of tiles): the right part of the 128 x 128 tile would be all padding, so the eight
+// consumer warps split the rows instead (16 rows x 8 NT columns each) and the DMMAs on the padding disappear (the POD lift
+// S W_c with c = retained + guard modes, the Gram matrix of the lifted modes).  A warp whose 16 rows lie beyond M (the
+// Gram matrix of c <= 96 columns) only releases the stages.
+template <int AMAJOR, int BMAJOR, int NT>
 __global__ void __launch_bounds__(THREADS, 1)
 k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
     extern __shared__ unsigned char smem_raw[];
@@ -207,7 +209,8 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
     asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
     const int cw = warp - PRODUCER_WARPS;
     const int g = lane >> 2, tig = lane & 3;
-    constexpr int MI_ = NARROW ? 2 : MI;
+    constexpr bool NARROW = NT > 0;
+    constexpr int MI_ = NARROW ? 2 : MI, NI_ = NARROW ? NT : NI;
     const int wm0 = NARROW ? cw * 16 : (cw / WARPS_N) * (MI * 8), wn0 = NARROW ? 0 : (cw % WARPS_N) * (NI * 8);
     // Fragment addresses as 32-bit shared-space offsets (LDS with immediate offsets instead of generic 64-bit
     // loads).  For k-step s the thread reads k index kq = 8*(tig>>1) + 2*((tig+s)&3) + (tig&1); in both majors rows
@@ -224,7 +227,7 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
         b_off[1][s] = TILE_BYTES + frag_off<BMAJOR>(wn0 + 8 + g, kq);
     }
 
-    double acc[MI_][NI][2];
+    double acc[MI_][NI_][2];
     int stage = 0;
     uint32_t phase = 0;
     for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
@@ -237,10 +240,12 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
 #pragma unroll
         for (int i = 0; i < MI_; ++i)
 #pragma unroll
-            for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+            for (int j = 0; j < NI_; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        // narrow tiles: rows of this warp beyond M are padding (TMA zero fill) -- nothing to multiply, nothing to store
+        const bool idle = NARROW && (int64_t)tm * BM + wm0 >= p.M;
 
         for (int kt = kt0; kt < kt1; ++kt) {
-            if (kt == p.hook_kt) {
+            if constexpr (NT == 0 || NT == NI) if (kt == p.hook_kt) {
                 if (p.hook_w) {
                     const int r = 2 * tn + (wn0 >> 6);
                     // one row of accumulator tiles at a time: its 8 loads are issued back to back (volatile asm keeps them
@@ -277,24 +282,26 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
             }
             mbar_wait(&full[stage], phase);
             const uint32_t st_addr = smem_base + stage * STAGE_BYTES;
+            if (!idle) {
 #pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                double af[MI_], bf[NI];
+                for (int s = 0; s < 4; ++s) {
+                    double af[MI_], bf[NI_];
 #pragma unroll
-                for (int i = 0; i < MI_; ++i) af[i] = lds_f64(st_addr + a_off[i & 1][s] + (uint32_t)(i >> 1) * 2048u);
+                    for (int i = 0; i < MI_; ++i) af[i] = lds_f64(st_addr + a_off[i & 1][s] + (uint32_t)(i >> 1) * 2048u);
 #pragma unroll
-                for (int j = 0; j < NI; ++j) bf[j] = lds_f64(st_addr + b_off[j & 1][s] + (uint32_t)(j >> 1) * 2048u);
+                    for (int j = 0; j < NI_; ++j) bf[j] = lds_f64(st_addr + b_off[j & 1][s] + (uint32_t)(j >> 1) * 2048u);
 #pragma unroll
-                for (int i = 0; i < MI_; ++i)
+                    for (int i = 0; i < MI_; ++i)
 #pragma unroll
-                    for (int j = 0; j < NI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                        for (int j = 0; j < NI_; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         double* Cout = p.C + (int64_t)split * p.split_stride;
-        store_acc(acc, Cout, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, p.alpha);
+        if (!idle) store_acc(acc, Cout, p.ldc_m, p.ldc_n, p.M, p.N, (int64_t)tm * BM + wm0, (int64_t)tn * BN + wn0, g, tig, p.alpha);
     }
 }
 
@@ -355,9 +362,9 @@ inline int make_map(rt_handle* h, const Operand& op, CUtensorMap* map) {
     return RT_OK;
 }
 
-template <int AMAJOR, int BMAJOR, bool NARROW>
+template <int AMAJOR, int BMAJOR, int NT>
 inline int launch_n(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
-    auto fn = k_dgemm<AMAJOR, BMAJOR, NARROW>;
+    auto fn = k_dgemm<AMAJOR, BMAJOR, NT>;
     RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     fn<<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p);
     RT_LAUNCH_CHECK(h);
@@ -366,8 +373,14 @@ inline int launch_n(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, 
 
 template <int AMAJOR, int BMAJOR>
 inline int launch_t(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
-    if (p.N <= 64 && !p.symmetric) return launch_n<AMAJOR, BMAJOR, true>(h, ma, mb, p, grid, st);
-    return launch_n<AMAJOR, BMAJOR, false>(h, ma, mb, p, grid, st);
+    // one column of tiles: the narrow instantiations (a symmetric product with a single tile is one too; the accumulator
+    // hook exists in the 64-column one only, as before)
+    if (p.tiles_n == 1 && (!p.symmetric || p.tiles_m == 1)) {
+        if (p.N <= 64) return launch_n<AMAJOR, BMAJOR, 8>(h, ma, mb, p, grid, st);
+        if (p.hook_kt < 0 && p.N <= 80) return launch_n<AMAJOR, BMAJOR, 10>(h, ma, mb, p, grid, st);
+        if (p.hook_kt < 0 && p.N <= 96) return launch_n<AMAJOR, BMAJOR, 12>(h, ma, mb, p, grid, st);
+    }
+    return launch_n<AMAJOR, BMAJOR, 0>(h, ma, mb, p, grid, st);
 }
 
 // C = alpha * A B^T-style product of two "mn x k" operands.  `p` carries C, strides, split and hook

@@ -26,7 +26,9 @@ int gemm_tn(rt_handle* h, const dg::Operand& A, const dg::Operand& B, double* C,
     const int tiles_m = (int)ceil_div64(A.mn, dg::BM), tiles_n = (int)ceil_div64(B.mn, dg::BN);
     const int ntiles = symmetric ? tiles_n * (tiles_n + 1) / 2 : tiles_m * tiles_n;
     const int kt_total = (int)ceil_div64(A.k, dg::BK);
-    const int splits = dg::choose_splits(ntiles, kt_total, h->sm_count, A.mn * B.mn);
+    // few output tiles (the Gram matrix of the lifted modes is ONE): as many k-splits as it takes to put two units on every SM
+    const int max_splits = ntiles * 64 >= 2 * h->sm_count ? 64 : (2 * h->sm_count + ntiles - 1) / ntiles;
+    const int splits = dg::choose_splits(ntiles, kt_total, h->sm_count, A.mn * B.mn, max_splits);
     p.symmetric = symmetric ? 1 : 0;
     p.splits = splits;
     if (splits == 1) {
