@@ -106,6 +106,17 @@ int rt_sym_eig_f64(rt_handle* h, double* G, int64_t n, double* w, double* W, int
 int rt_sym_eig_jacobi_f64(rt_handle* h, const double* A, int64_t n, double* w, double* W, int* info,
                           double* defect, void* stream);
 
+/* rt_sym_eig_jacobi_static_f64: rt_sym_eig_jacobi_f64 for callers that may not allocate.  No counterpart in the reference:
+ * added (callers under CUDA-graph capture set-up, tight serving loops and harnesses
+ * that forbid cudaMalloc).  Same arguments, same results; the work space is a fixed device array inside the library
+ * (static __device__, about 322 KB, held by every GPU that loads the library until exit), so n <= 128
+ * (RT_STATIC_EIG_MAX_N) -- a larger n returns RT_EINVAL with a message naming the limit.  The call makes no cudaMalloc /
+ * cudaFree and calls no allocating library routine.  All calls on a device share the array: calls that overlap on the GPU
+ * (two streams, two host threads) race and must be serialised by the caller; nothing in it survives between calls. */
+#define RT_STATIC_EIG_MAX_N 128
+int rt_sym_eig_jacobi_static_f64(rt_handle* h, const double* A, int64_t n, double* w, double* W, int* info,
+                                 double* defect, void* stream);
+
 /* Basis lift  Q = S Wr  (Nh x r): left singular vectors from the Gram eigenvectors,
  * Wr (n x r, row-major, leading dimension ldw) already scaled by 1/(sigma_k * colnorm_j).
  * Q is written with strides (q_stride_row, q_stride_col). */

@@ -59,6 +59,7 @@ SIGNATURES = {
     "rt_gram_finalize_f64": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp, c_vp]),
     "rt_sym_eig_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "rt_sym_eig_jacobi_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "rt_sym_eig_jacobi_static_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rt_deflate_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "rt_pod_lift_f64": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_i64, c_vp]),
     "rt_small_gram_eig_f64": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp]),

@@ -653,3 +653,94 @@ extern "C" int rt_sym_eig_jacobi_f64(rt_handle* h, const double* A, int64_t n, d
     RT_CUDA(h, cudaStreamSynchronize(st));
     return RT_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// rt_sym_eig_jacobi_static_f64: the plain block Jacobi of rt_sym_eig_jacobi_f64 for callers that may not allocate (code under
+// CUDA-graph capture set-up, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Its work space (padded copy of the matrix, rotation product, sub-problem rotations,
+// counters, ordering) lives in ONE file-scope device array of fixed size, so the order is limited to kStaticEigMaxN.
+// Every GPU that loads the library holds the array (about 322 KB) until exit; all calls on a device share it, so calls that
+// overlap on the GPU (different streams, different host threads) race -- serialise them.  Nothing in it has to survive
+// between calls: every call rewrites the padded matrix and the identity, and clears its rotation counter.
+constexpr int kStaticEigMaxN = 128;
+constexpr int64_t kStaticPad = (kStaticEigMaxN + TS - 1) / TS * TS;               // 128
+constexpr int kStaticPairs = (int)(kStaticPad / BS / 2);                           // 2 sub-problems per round
+constexpr size_t kStaticDoubles = 2 * kStaticPad * kStaticPad + (size_t)kStaticPairs * TS * TS + 16;
+constexpr size_t kStaticBytes = kStaticDoubles * sizeof(double) + kStaticEigMaxN * sizeof(int);
+static __device__ __align__(256) unsigned char g_static_eig_scratch[kStaticBytes];
+
+// In host code the array's name is only a stand-in: the device address comes from cudaGetSymbolAddress, once per device,
+// with that device current.
+static int static_eig_scratch(rt_handle* h, unsigned char** out) {
+    constexpr int kMaxDevices = 64;
+    static unsigned char* addr[kMaxDevices] = {nullptr};
+    if (h->device < 0 || h->device >= kMaxDevices) return rt_fail(h, RT_EINVAL, "device index %d beyond %d", h->device, kMaxDevices);
+    if (!addr[h->device]) {
+        void* p = nullptr;
+        RT_CUDA(h, cudaGetSymbolAddress(&p, g_static_eig_scratch));
+        if (!p) return rt_fail(h, RT_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+        addr[h->device] = (unsigned char*)p;
+    }
+    *out = addr[h->device];
+    return RT_OK;
+}
+
+extern "C" int rt_sym_eig_jacobi_static_f64(rt_handle* h, const double* Ain, int64_t n, double* w, double* W, int* info,
+                                            double* defect, void* stream) {
+    if (!h) return RT_EINVAL;
+    RT_REQUIRE(h, Ain && w && W && n >= 1);
+    if (n > kStaticEigMaxN)
+        return rt_fail(h, RT_EINVAL, "rt_sym_eig_jacobi_static_f64: n = %lld exceeds the static work space (n <= %d); "
+                       "use rt_sym_eig_jacobi_f64", (long long)n, kStaticEigMaxN);
+    RT_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = rt_stream(stream);
+    unsigned char* base;
+    int rc = static_eig_scratch(h, &base);
+    if (rc) return rc;
+    const int64_t npad = ceil_div64(n, TS) * TS;
+    const int nb = (int)(npad / BS), P = nb / 2;
+    double* A = (double*)base;
+    double* V = A + npad * npad;
+    double* Wbuf = V + npad * npad;
+    double* maxdiag = Wbuf + (size_t)P * TS * TS;
+    unsigned long long* counter = (unsigned long long*)(maxdiag + 1);
+    int* rank = (int*)(base + kStaticDoubles * sizeof(double));
+
+    if (defect) {
+        RT_CUDA(h, cudaMemsetAsync(defect, 0, sizeof(double), st));
+        k_scaled_defect<<<(unsigned)n, 256, 0, st>>>(Ain, n, n, defect);
+        RT_LAUNCH_CHECK(h);
+    }
+    k_pad_copy<<<dim3((unsigned)ceil_div64(npad, 256), (unsigned)npad), 256, 0, st>>>(Ain, n, n, A, V, npad);
+    RT_LAUNCH_CHECK(h);
+    k_maxdiag<<<1, 256, 0, st>>>(A, n, npad, maxdiag);
+    RT_LAUNCH_CHECK(h);
+    const int apply_smem = 3 * TS * LDS_ * (int)sizeof(double);
+    RT_CUDA(h, cudaFuncSetAttribute(k_jacobi_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, apply_smem));
+    const int sub_smem = 2 * TS * (TS + 1) * (int)sizeof(double);
+    RT_CUDA(h, cudaFuncSetAttribute(k_jacobi_sub, cudaFuncAttributeMaxDynamicSharedMemorySize, sub_smem));
+    const int nA = P * (P - 1) / 2, nV = (int)(npad / TS) * P;
+    const int rounds = nb - 1, max_sweeps = 60;
+    int sweeps = -1;
+    for (int sweep = 0; sweep < max_sweeps; ++sweep) {
+        RT_CUDA(h, cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st));
+        for (int round = 0; round < rounds; ++round) {
+            k_jacobi_sub<<<P, kSubThreads, sub_smem, st>>>(A, npad, round, nb, Wbuf, counter, maxdiag, 0.0);
+            RT_LAUNCH_CHECK(h);
+            k_jacobi_apply<<<nA + nV, 256, apply_smem, st>>>(A, V, npad, round, nb, Wbuf, nA);
+            RT_LAUNCH_CHECK(h);
+        }
+        unsigned long long rot = 0;
+        RT_CUDA(h, cudaMemcpyAsync(&rot, counter, sizeof(rot), cudaMemcpyDeviceToHost, st));
+        RT_CUDA(h, cudaStreamSynchronize(st));
+        if ((rot >> 32) == 0) { sweeps = sweep + 1; break; }
+    }
+    k_rank<<<(unsigned)ceil_div64(n, 128), 128, 0, st>>>(A, n, npad, rank, w);
+    RT_LAUNCH_CHECK(h);
+    k_scatter_vectors<<<dim3((unsigned)ceil_div64(n, 32), (unsigned)ceil_div64(n, 32)), dim3(32, 8), 0, st>>>(V, n, npad, rank, W, n);
+    RT_LAUNCH_CHECK(h);
+    if (sweeps < 0) return rt_fail(h, RT_ENOTCONV, "block Jacobi did not converge in %d sweeps (n=%lld)", max_sweeps, (long long)n);
+    if (info) RT_CUDA(h, cudaMemcpyAsync(info, &sweeps, sizeof(int), cudaMemcpyHostToDevice, st));
+    RT_CUDA(h, cudaStreamSynchronize(st));
+    return RT_OK;
+}
