@@ -43,6 +43,26 @@ def _stale():
     return any(os.path.getmtime(p) > t for p in deps)
 
 
+# The shipped assembly GEMM (k_dgemm<MN, MN, full tile>) carries ONE 4-byte spill slot and is bitwise reproducible in every
+# parity test.  Builds of the same kernel with a few hundred bytes of spills have produced corrupted 8-row blocks twice (the
+# deferred-store experiment of round 1; the 5-stage / 200-register variant of round 2 when it shared an SM with the solve
+# kernel), so such a build is not linked.
+MAX_GEMM_SPILL_BYTES = 16
+
+
+def _spilling_gemm_kernels(ptxas_log):
+    """dg::k_dgemm instantiations for which ptxas -v reports more than MAX_GEMM_SPILL_BYTES of spill stores."""
+    bad, current = [], None
+    for line in ptxas_log.splitlines():
+        if "Compiling entry function" in line:
+            current = line.split("'")[1] if "'" in line else line
+        elif "bytes spill stores" in line and current and "k_dgemm" in current:
+            nums = [int(tok) for tok in line.replace(",", " ").split() if tok.isdigit()]
+            if len(nums) >= 3 and nums[1] > MAX_GEMM_SPILL_BYTES:
+                bad.append(f"{current}: {nums[1]} bytes of spill stores")
+    return bad
+
+
 def build_library(force=False, verbose=False):
     """Compile every csrc/*.cu into one shared object. Returns the library path."""
     if not force and not _stale():
@@ -55,7 +75,7 @@ def build_library(force=False, verbose=False):
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + os.environ.get("RT_NVCC_EXTRA", "").split() + ["-Xptxas", "-v", "-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for src, p in procs:
@@ -63,8 +83,17 @@ def build_library(force=False, verbose=False):
         if p.returncode != 0:
             failed = True
             sys.stderr.write(f"nvcc failed on {src}:\n{out}\n")
-        elif verbose or "warning" in out:
-            sys.stderr.write(out)
+        else:
+            if verbose:
+                sys.stderr.write(out)
+            else:
+                sys.stderr.write("".join(l + "\n" for l in out.splitlines() if "warning" in l and "ptxas info" not in l))
+            spilled = _spilling_gemm_kernels(out)
+            if spilled and os.environ.get("RT_ALLOW_GEMM_SPILLS") != "1":
+                failed = True
+                sys.stderr.write(f"{src}: register spills in the GEMM core ({', '.join(spilled)}): heavily spilling builds of "
+                                 "dg::k_dgemm have produced corrupted 8-row blocks (DESIGN.md 4.1); refusing to link it "
+                                 "(RT_ALLOW_GEMM_SPILLS=1 overrides, for experiments)\n")
     if failed:
         raise RuntimeError("nvcc compilation failed")
     link = [nvcc, "-shared", "-cudart", "static", "-o", LIB] + objs + ["-ldl", "-lpthread", "-lrt"]

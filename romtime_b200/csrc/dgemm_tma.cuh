@@ -24,7 +24,20 @@ namespace dg {
 enum { MAJOR_K = 0, MAJOR_MN = 1 };
 
 constexpr int BM = 128, BN = 128, BK = 16;
-constexpr int STAGES = 6;
+#ifndef RT_GEMM_STAGES
+#define RT_GEMM_STAGES 6
+#endif
+#ifndef RT_GEMM_CONSUMER_REGS
+#define RT_GEMM_CONSUMER_REGS 240
+#endif
+#define RT_STR2(x) #x
+#define RT_STR(x) RT_STR2(x)
+#ifdef RT_GEMM_LAUNCH_REGS
+#define RT_GEMM_BOUNDS __maxnreg__(RT_GEMM_LAUNCH_REGS)
+#else
+#define RT_GEMM_BOUNDS __launch_bounds__(THREADS, 1)
+#endif
+constexpr int STAGES = RT_GEMM_STAGES;
 constexpr int CONSUMER_WARPS = 8;
 constexpr int PRODUCER_WARPS = 4;                // one warpgroup; lane 0 of its first warp issues TMA
 constexpr int THREADS = (CONSUMER_WARPS + PRODUCER_WARPS) * 32;
@@ -150,7 +163,7 @@ __device__ __forceinline__ void store_acc(const double (&acc)[MI_][NI_][2], doub
 // S W_c with c = retained + guard modes, the Gram matrix of the lifted modes).  A warp whose 16 rows lie beyond M (the
 // Gram matrix of c <= 96 columns) only releases the stages.
 template <int AMAJOR, int BMAJOR, int NT>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void RT_GEMM_BOUNDS
 k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -206,7 +219,7 @@ k_dgemm(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtens
     }
 
     // ===================== DMMA consumers (two warpgroups) =====================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 " RT_STR(RT_GEMM_CONSUMER_REGS) ";");
     const int cw = warp - PRODUCER_WARPS;
     const int g = lane >> 2, tig = lane & 3;
     constexpr bool NARROW = NT > 0;
@@ -366,6 +379,9 @@ template <int AMAJOR, int BMAJOR, int NT>
 inline int launch_n(rt_handle* h, const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t st) {
     auto fn = k_dgemm<AMAJOR, BMAJOR, NT>;
     RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+#ifdef RT_GEMM_LAUNCH_REGS
+    RT_CUDA(h, cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+#endif
     fn<<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p);
     RT_LAUNCH_CHECK(h);
     return RT_OK;

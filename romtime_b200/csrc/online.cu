@@ -735,7 +735,7 @@ __device__ __forceinline__ void gjs_subpanel(GjsShared& sh, int T, int h, double
         sh.gr[4 * h + lane] = g;
         reinterpret_cast<double*>(sh.tiles)[64 * T + gjs_rowoff(g, 4 * h + lane)] = rv;
         sh.colof[g] = (unsigned char)(8 * T + 4 * h + lane);
-        if (!(fabs(rv) < 1.7976931348623157e308)) atomicCAS(info_p + blockIdx.x, 0, step + 1);
+        if (!(fabs(rv) < 1.7976931348623157e308)) atomicCAS(info_p, 0, step + 1);
     }
 }
 
@@ -865,13 +865,17 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
                                                     const double* __restrict__ From, const double* __restrict__ Wv, LuExtras ex,
                                                     double* __restrict__ Un, double* __restrict__ Unm1,
                                                     double* __restrict__ uN_out, int64_t out_stride_p, int64_t out_off,
-                                                    int* __restrict__ info, int step) {
+                                                    int* __restrict__ info_all, int step) {
     __shared__ __align__(16) GjsShared sh;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int g8 = lane >> 2, q = lane & 3;
     const int N = pl.N;
     const bool vec = (N & 1) == 0;
-    const int64_t p = blockIdx.x;
+    // one system per CTA (grid = Bc) or a persistent grid that strides over the chunk (one CTA per SM beside the assembly
+    // GEMM of the other lane, sweep_impl)
+#pragma unroll 1
+    for (int64_t p = blockIdx.x; p < pl.Bc; p += gridDim.x) {
+    int* info = info_all + p;
     const double* Kp = Kmat + p * pl.ldk;
     const double* Mp = Mmat + p * pl.ldk;
     const double* Ka = ex.Kadd ? ex.Kadd + p * N * N : nullptr;
@@ -947,7 +951,7 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
     }
     __syncthreads();
 
-    const int rot = (int)(blockIdx.x & 3);
+    const int rot = (int)(p & 3);
     if (w == rot) gjs_factor(sh, 0, lane, false, info, step);
     __syncthreads();
 #pragma unroll 1
@@ -990,6 +994,8 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
             Un[s] = x;
             if (uN_out) uN_out[p * out_stride_p + out_off + c] = x;
         }
+    }
+    __syncthreads();  // the next system of a persistent CTA re-uses sh
     }
 }
 
@@ -1160,7 +1166,12 @@ inline bool mw_in_gemm(const SweepPlan& pl, const LuExtras& ex) {
 }
 
 int launch_gj(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o, cudaStream_t st) {
-    k_gj_smem<<<pl.Bc, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw_in_gemm(pl, ex) ? b.Mw : nullptr, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out,
+#ifdef RT_GEMM_LAUNCH_REGS
+    RT_CUDA(h, cudaFuncSetAttribute(k_gj_smem, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+#endif
+    int gj_grid = pl.Bc;
+    if (getenv("RT_GJ_GRID")) { gj_grid = atoi(getenv("RT_GJ_GRID")); if (gj_grid > pl.Bc) gj_grid = pl.Bc; }
+    k_gj_smem<<<gj_grid, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw_in_gemm(pl, ex) ? b.Mw : nullptr, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out,
                                      o.stride_p, o.off, o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
