@@ -239,3 +239,41 @@ def test_small_eig_kernels_against_lapack():
         assert np.max(np.abs(np.sqrt(lam) - sv) / sv) < 1e-12          # relative, on a spectrum spanning 1e-12
         assert np.max(np.abs(X.T @ X - np.eye(c))) < 1e-13
         assert 1e-5 < float(defect[j].item()) < 1e-2
+
+
+@pytest.mark.parametrize("c", [8, 57, 64, 65, 72, 80, 81, 96, 97])
+@pytest.mark.parametrize("order", ["C", "F"])
+def test_lift_narrow_tiles_against_torch(c, order):
+    """The GEMM core's narrow instantiations (one column of tiles, 64 / 80 / 96 columns per warp row) and the full tile next
+    to them: Q = S W for ragged row counts against torch's fp64 matmul."""
+    import torch
+
+    from romtime_b200 import kernels
+
+    g = torch.Generator(device="cuda").manual_seed(c)
+    S = torch.randn((20_011, 133), dtype=torch.float64, device="cuda", generator=g)
+    W = torch.randn((133, c), dtype=torch.float64, device="cuda", generator=g)
+    Q = kernels.pod_lift(S, W, order=order)
+    ref = S @ W
+    assert Q.shape == ref.shape
+    assert (Q - ref).abs().max().item() < 1e-11 * ref.abs().max().item() * 133 ** 0.5
+
+
+@pytest.mark.parametrize("n", [5, 64, 72, 96, 100])
+def test_gram_of_few_columns_deep_split(n):
+    """Gram matrix of a tall matrix with ONE output tile: the k-range is split over the whole GPU (deterministic fixed-order
+    reduction of the partial tiles), narrow tiles for n <= 96."""
+    import torch
+
+    from romtime_b200 import kernels
+
+    g = torch.Generator(device="cuda").manual_seed(n)
+    Y = torch.randn((300_007, n), dtype=torch.float64, device="cuda", generator=g) * torch.pow(
+        10.0, -torch.arange(n, dtype=torch.float64, device="cuda") / 8.0)
+    H = kernels.pod_gram(Y, normalize=False)[0]
+    H2 = kernels.pod_gram(Y, normalize=False)[0]
+    assert torch.equal(H, H2)                      # bitwise reproducible
+    assert torch.equal(H, H.t())                   # exactly symmetric
+    ref = Y.t() @ Y
+    scale = torch.sqrt(torch.outer(torch.diag(ref), torch.diag(ref)))
+    assert ((H - ref).abs() / scale).max().item() < 1e-12
