@@ -330,6 +330,150 @@ __global__ void __launch_bounds__(256) k_forcing(SweepPlan pl, const double* __r
     }
 }
 
+// ------------------------------------------------------------------ fused pre-step (N <= 64, m_tril <= 128, m_rhs <= 128)
+// k_state + k_tu + k_entries + k_forcing of one time step in ONE persistent kernel on the FP64 tensor pipe.  A CTA keeps T
+// (trilinear table) and rhs_til (folded forcing basis) in shared memory and walks over blocks of 32 parameters:
+//   (a) phi(mu_p, t), u*_p, w_p (w goes to global memory for the assembly GEMM's M w hook);
+//   (b) F[q][p] = scale_op ( C[q][:] phi_p  +  [trilinear rows] T[q][:] (b0_p u*_p) )  as DMMA tiles of 8 rows x 8 parameters
+//       (3 k-steps for the 12 features, Npad / 4 more for the trilinear rows); the rows of the forcing operator stay in
+//       shared memory, the others are the A operand of the assembly GEMM;
+//   (c) From[p][:] = rhs_til^T F_rhs[:, p]  (reduced forcing).
+// The four separate kernels took 116 us per 14,208-parameter step (each a launch with its own staging, 1.5 waves of CTAs,
+// scalar FMAs fed by broadcast shared-memory loads); this one is bound by 3,200 DMMAs per block.
+constexpr int kPreLd = 68;    // rows of T / rhs_til / u*: 68 == 4 (mod 16), conflict-free DMMA fragments in both orientations
+constexpr int kPreLdp = 36;   // rows of the [k][32 parameters] operands (phi, F_rhs): 36 == 4 (mod 16)
+constexpr int kPreBlock = 32;
+constexpr size_t kPreSmemBytes = ((size_t)2 * 128 * kPreLd + (size_t)kPreBlock * kPreLd + (size_t)RT_NF * kPreLdp +
+                                  (size_t)128 * kPreLdp) * sizeof(double);
+
+__device__ __forceinline__ void pre_dmma(double (&c)[2], double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* __restrict__ mu, double t, int have_prev, int bdf2,
+                                                    const double* __restrict__ Un, const double* __restrict__ Unm1,
+                                                    const double* __restrict__ Ccat, const double* __restrict__ Tpad,
+                                                    const double* __restrict__ rhs_til, double dt, double* __restrict__ Wv,
+                                                    double* __restrict__ F, double* __restrict__ From) {
+    extern __shared__ __align__(16) double sm_pre[];
+    double* Ts = sm_pre;                          // 128 x kPreLd   T[q][j], zero beyond (m_tril, Npad)
+    double* Rs = Ts + 128 * kPreLd;               // 128 x kPreLd   rhs_til[k][i]
+    double* us = Rs + 128 * kPreLd;               // 32 x kPreLd    b0_p u*_p[j]
+    double* phis = us + kPreBlock * kPreLd;       // RT_NF x kPreLdp  phi[f][p]
+    double* fs = phis + RT_NF * kPreLdp;          // 128 x kPreLdp  F_rhs[k][p]
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, g = lane >> 2, tig = lane & 3;
+    const int Np = pl.Npad, N = pl.N;
+    const int mT = Tpad ? pl.m[kTril] : 0, mR = rhs_til ? pl.mpad[kRhs] : 0;
+    for (int e = tid; e < 128 * 64; e += 256) {
+        const int r = e >> 6, j = e & 63;
+        Ts[r * kPreLd + j] = (r < mT && j < Np) ? Tpad[r * Np + j] : 0.0;
+        Rs[r * kPreLd + j] = (r < mR && j < Np) ? rhs_til[r * Np + j] : 0.0;
+    }
+    const int ksteps_u = (Np + 3) / 4;            // k-steps over the reduced dimension
+    const int qtiles = pl.Qall / 8;
+    const int nblk = (pl.Bc + kPreBlock - 1) / kPreBlock;
+    for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        const int64_t p0 = (int64_t)blk * kPreBlock;
+        // ---- (a) features, then u* (scaled by b0 = phi[11], the trilinear coefficient) and w
+        if (tid < kPreBlock) {
+            double phi[RT_NF];
+#pragma unroll
+            for (int f = 0; f < RT_NF; ++f) phi[f] = 0.0;
+            if (p0 + tid < pl.Bc) {
+                const double* m = mu + (p0 + tid) * pl.n_mu;
+                if (pl.evaluator == 2) mfp1_features(m[0], m[1], m[2], m[3], t, phi);
+                else piston_features(pl.evaluator, m[0], m[1], m[2], t, phi);
+            }
+#pragma unroll
+            for (int f = 0; f < RT_NF; ++f) phis[f * kPreLdp + tid] = phi[f];
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int e = tid; e < kPreBlock * 64; e += 256) {
+            const int r = e >> 6, j = e & 63;
+            const int64_t p = p0 + r;
+            double un = 0.0, um = 0.0;
+            if (p < pl.Bc && j < N) { un = Un[p * pl.ldu + j]; um = Unm1[p * pl.ldu + j]; }
+            const double ustar = have_prev ? 2.0 * un - um : un;
+            us[r * kPreLd + j] = phis[11 * kPreLdp + r] * ustar;
+            if (p < pl.Bc && j < Np) Wv[p * Np + j] = bdf2 ? 2.0 * un - 0.5 * um : un;
+        }
+        __syncthreads();
+        // ---- (b) sampled entries: q-tile qt = 8 rows, all 32 parameters (4 tiles of 8)
+        double cfrag[RT_NF / 4];   // C fragment of the warp's next q-tile, loaded one tile ahead (L2 latency off the chain)
+        if (w < qtiles) {
+#pragma unroll
+            for (int ks = 0; ks < RT_NF / 4; ++ks) cfrag[ks] = __ldg(Ccat + (int64_t)(8 * w + g) * RT_NF + tig + 4 * ks);
+        }
+        for (int qt = w; qt < qtiles; qt += 8) {
+            const int q0 = 8 * qt;
+            int op = 0;
+            while (q0 >= pl.qoff[op + 1]) ++op;
+            double acc[4][2];
+#pragma unroll
+            for (int jn = 0; jn < 4; ++jn) acc[jn][0] = acc[jn][1] = 0.0;
+            double ca[RT_NF / 4];
+#pragma unroll
+            for (int ks = 0; ks < RT_NF / 4; ++ks) ca[ks] = cfrag[ks];
+            if (qt + 8 < qtiles) {
+#pragma unroll
+                for (int ks = 0; ks < RT_NF / 4; ++ks) cfrag[ks] = __ldg(Ccat + (int64_t)(q0 + 64 + g) * RT_NF + tig + 4 * ks);
+            }
+#pragma unroll
+            for (int ks = 0; ks < RT_NF / 4; ++ks) {
+#pragma unroll
+                for (int jn = 0; jn < 4; ++jn) pre_dmma(acc[jn], ca[ks], phis[(4 * ks + tig) * kPreLdp + 8 * jn + g]);
+            }
+            if (op == kTril && mT > 0) {
+                const double* trow = Ts + (q0 - pl.qoff[kTril] + g) * kPreLd + tig;
+#pragma unroll 4
+                for (int ks = 0; ks < ksteps_u; ++ks) {
+                    const double a = trow[4 * ks];
+#pragma unroll
+                    for (int jn = 0; jn < 4; ++jn) pre_dmma(acc[jn], a, us[(8 * jn + g) * kPreLd + 4 * ks + tig]);
+                }
+            }
+            const double scale = op == 0 ? 1.0 : dt;
+            if (op == kRhs) {
+                double* frow = fs + (q0 - pl.qoff[kRhs] + g) * kPreLdp + 2 * tig;
+#pragma unroll
+                for (int jn = 0; jn < 4; ++jn)
+                    *reinterpret_cast<double2*>(frow + 8 * jn) = make_double2(acc[jn][0] * scale, acc[jn][1] * scale);
+            } else {
+                double* frow = F + (int64_t)(q0 + g) * pl.Bcpad + p0 + 2 * tig;
+#pragma unroll
+                for (int jn = 0; jn < 4; ++jn)
+                    if (p0 + 8 * jn + 2 * tig < pl.Bc)
+                        *reinterpret_cast<double2*>(frow + 8 * jn) = make_double2(acc[jn][0] * scale, acc[jn][1] * scale);
+            }
+        }
+        __syncthreads();
+        // ---- (c) reduced forcing: rows i of From^T, 8 per warp
+        if (mR > 0 && 8 * w < Np) {
+            double acc[4][2];
+#pragma unroll
+            for (int jn = 0; jn < 4; ++jn) acc[jn][0] = acc[jn][1] = 0.0;
+            const double* rcol = Rs + tig * kPreLd + 8 * w + g;
+#pragma unroll 4
+            for (int ks = 0; ks < mR / 4; ++ks) {
+                const double a = rcol[4 * ks * kPreLd];
+#pragma unroll
+                for (int jn = 0; jn < 4; ++jn) pre_dmma(acc[jn], a, fs[(4 * ks + tig) * kPreLdp + 8 * jn + g]);
+            }
+            const int i = 8 * w + g;
+            if (i < Np) {
+#pragma unroll
+                for (int jn = 0; jn < 4; ++jn) {
+                    const int64_t p = p0 + 8 * jn + 2 * tig;
+                    if (p < pl.Bc) From[p * Np + i] = acc[jn][0];
+                    if (p + 1 < pl.Bc) From[(p + 1) * Np + i] = acc[jn][1];
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------ dense LU solve per parameter
 // One CTA per parameter: K (N x N) and the right-hand side b = M w + f as an augmented column in
 // shared memory, LU with partial pivoting (dgesv-like, replaces GMRES rom.py:36/:492), back
@@ -1355,6 +1499,20 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     const int64_t nstate = (int64_t)pl.Bc * pl.Npad;
     Profile* prof = (Profile*)h->profile;
     const bool pa = prof && prof->on && profiled;
+    // state, trilinear product, sampled entries and reduced forcing in one kernel when the tables fit its shared memory
+    const bool fused = !Fext && mu_c && pl.Npad <= 64 && (!cx.has_T || pl.m[kTril] <= 128) && pl.mpad[kRhs] <= 128 &&
+                       pl.Qmat > 0 && !(getenv("RT_FUSED_PRESTEP") && atoi(getenv("RT_FUSED_PRESTEP")) == 0);
+    if (fused) {
+        ProfScope ps(prof, pa, 2, st);
+        rc = rt_ensure_smem(h, 11, k_prestep, (int)kPreSmemBytes);
+        if (rc) return rc;
+        int grid = (pl.Bc + kPreBlock - 1) / kPreBlock;
+        if (grid > h->sm_count) grid = h->sm_count;
+        k_prestep<<<grid, 256, kPreSmemBytes, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Ccat,
+                                                   cx.has_T ? b.Tpad : nullptr, pl.m[kRhs] > 0 ? b.rhs_til : nullptr, dt, b.Wv, b.F,
+                                                   b.From);
+        RT_LAUNCH_CHECK(h);
+    } else {
     {
         ProfScope ps(prof, pa, 0, st);
         k_state<<<(unsigned)ceil_div64(nstate, 256), 256, 0, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Phi, b.Ustar,
@@ -1388,6 +1546,7 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
         k_entries<<<egrid2, 128, 0, st>>>(pl, b.Ccat, b.Phi, cx.has_T ? b.TU : nullptr, dt, b.F);
         RT_LAUNCH_CHECK(h);
     }
+    }  // !fused
     if (pl.Qmat > 0) {
         ProfScope ps(prof, pa, 4, st);  // K = bdf M + dt (A + C + N^ + N(u*)),  M emitted at the k-boundary
         dg::Operand oa{b.F, pl.Bc, pl.Qmat, 1, pl.Bcpad}, ob{b.basis_til, pl.N2, pl.Qmat, 1, pl.ldk};
@@ -1410,7 +1569,9 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
         RT_CUDA(h, cudaMemsetAsync(b.Kmat, 0, (size_t)pl.Bc * pl.ldk * sizeof(double), st));
         RT_CUDA(h, cudaMemsetAsync(b.Mmat, 0, (size_t)pl.Bc * pl.ldk * sizeof(double), st));
     }
-    if (pl.m[kRhs] > 0) {
+    if (fused) {
+        if (pl.m[kRhs] == 0) RT_CUDA(h, cudaMemsetAsync(b.From, 0, (size_t)pl.Bc * pl.Npad * sizeof(double), st));
+    } else if (pl.m[kRhs] > 0) {
         ProfScope ps(prof, pa, 5, st);  // reduced forcing dt * basis_rhs theta_rhs
         if (pl.N <= 64 && pl.mpad[kRhs] <= 128) {
             rc = rt_ensure_smem(h, 10, k_forcing, (128 * 32 + 128 * 64) * 8);
