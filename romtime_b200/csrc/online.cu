@@ -350,7 +350,9 @@ __device__ __forceinline__ void pre_dmma(double (&c)[2], double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* __restrict__ mu, double t, int have_prev, int bdf2,
+constexpr int kPreThreads = 512;   // 16 warps: four per scheduler keep the DMMA pipe fed through the short chains of a q-tile
+
+__global__ void __launch_bounds__(kPreThreads, 1) k_prestep(SweepPlan pl, const double* __restrict__ mu, double t, int have_prev, int bdf2,
                                                     const double* __restrict__ Un, const double* __restrict__ Unm1,
                                                     const double* __restrict__ Ccat, const double* __restrict__ Tpad,
                                                     const double* __restrict__ rhs_til, double dt, double* __restrict__ Wv,
@@ -364,17 +366,38 @@ __global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, g = lane >> 2, tig = lane & 3;
     const int Np = pl.Npad, N = pl.N;
     const int mT = Tpad ? pl.m[kTril] : 0, mR = rhs_til ? pl.mpad[kRhs] : 0;
-    for (int e = tid; e < 128 * 64; e += 256) {
-        const int r = e >> 6, j = e & 63;
-        Ts[r * kPreLd + j] = (r < mT && j < Np) ? Tpad[r * Np + j] : 0.0;
-        Rs[r * kPreLd + j] = (r < mR && j < Np) ? rhs_til[r * Np + j] : 0.0;
+    {
+        // both tables with every load of a thread in flight at once (16 + 16 elements per thread)
+        constexpr int kPer = 128 * 64 / kPreThreads;
+        double tv[kPer], rv[kPer];
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int e = tid + i * kPreThreads, r = e >> 6, j = e & 63;
+            tv[i] = (r < mT && j < Np) ? __ldg(Tpad + r * Np + j) : 0.0;
+            rv[i] = (r < mR && j < Np) ? __ldg(rhs_til + r * Np + j) : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int e = tid + i * kPreThreads, r = e >> 6, j = e & 63;
+            Ts[r * kPreLd + j] = tv[i];
+            Rs[r * kPreLd + j] = rv[i];
+        }
     }
     const int ksteps_u = (Np + 3) / 4;            // k-steps over the reduced dimension
     const int qtiles = pl.Qall / 8;
     const int nblk = (pl.Bc + kPreBlock - 1) / kPreBlock;
     for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
         const int64_t p0 = (int64_t)blk * kPreBlock;
-        // ---- (a) features, then u* (scaled by b0 = phi[11], the trilinear coefficient) and w
+        // ---- (a) features, then u* (scaled by b0 = phi[11], the trilinear coefficient) and w; the state loads are issued
+        // first, their latency hides under the feature evaluation
+        double un_reg[kPreBlock * 64 / kPreThreads], um_reg[kPreBlock * 64 / kPreThreads];
+#pragma unroll
+        for (int i = 0; i < kPreBlock * 64 / kPreThreads; ++i) {
+            const int e = tid + i * kPreThreads, r = e >> 6, j = e & 63;
+            const bool in = p0 + r < pl.Bc && j < N;
+            un_reg[i] = in ? Un[(p0 + r) * pl.ldu + j] : 0.0;
+            um_reg[i] = in ? Unm1[(p0 + r) * pl.ldu + j] : 0.0;
+        }
         if (tid < kPreBlock) {
             double phi[RT_NF];
 #pragma unroll
@@ -388,15 +411,16 @@ __global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* 
             for (int f = 0; f < RT_NF; ++f) phis[f * kPreLdp + tid] = phi[f];
         }
         __syncthreads();
-#pragma unroll 2
-        for (int e = tid; e < kPreBlock * 64; e += 256) {
-            const int r = e >> 6, j = e & 63;
-            const int64_t p = p0 + r;
-            double un = 0.0, um = 0.0;
-            if (p < pl.Bc && j < N) { un = Un[p * pl.ldu + j]; um = Unm1[p * pl.ldu + j]; }
-            const double ustar = have_prev ? 2.0 * un - um : un;
-            us[r * kPreLd + j] = phis[11 * kPreLdp + r] * ustar;
-            if (p < pl.Bc && j < Np) Wv[p * Np + j] = bdf2 ? 2.0 * un - 0.5 * um : un;
+        {
+            constexpr int kPer = kPreBlock * 64 / kPreThreads;
+#pragma unroll
+            for (int i = 0; i < kPer; ++i) {
+                const int e = tid + i * kPreThreads, r = e >> 6, j = e & 63;
+                const double un = un_reg[i], um = um_reg[i];
+                const double ustar = have_prev ? 2.0 * un - um : un;
+                us[r * kPreLd + j] = phis[11 * kPreLdp + r] * ustar;
+                if (p0 + r < pl.Bc && j < Np) Wv[(p0 + r) * Np + j] = bdf2 ? 2.0 * un - 0.5 * um : un;
+            }
         }
         __syncthreads();
         // ---- (b) sampled entries: q-tile qt = 8 rows, all 32 parameters (4 tiles of 8)
@@ -405,19 +429,20 @@ __global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* 
 #pragma unroll
             for (int ks = 0; ks < RT_NF / 4; ++ks) cfrag[ks] = __ldg(Ccat + (int64_t)(8 * w + g) * RT_NF + tig + 4 * ks);
         }
-        for (int qt = w; qt < qtiles; qt += 8) {
+        for (int qt = w; qt < qtiles; qt += kPreThreads / 32) {
             const int q0 = 8 * qt;
-            int op = 0;
-            while (q0 >= pl.qoff[op + 1]) ++op;
+            // operator of the tile, from constant-index reads of the plan (a dynamic index would put the plan on the stack)
+            const int op = (q0 >= pl.qoff[1]) + (q0 >= pl.qoff[2]) + (q0 >= pl.qoff[3]) + (q0 >= pl.qoff[4]) + (q0 >= pl.qoff[5]);
             double acc[4][2];
 #pragma unroll
             for (int jn = 0; jn < 4; ++jn) acc[jn][0] = acc[jn][1] = 0.0;
             double ca[RT_NF / 4];
 #pragma unroll
             for (int ks = 0; ks < RT_NF / 4; ++ks) ca[ks] = cfrag[ks];
-            if (qt + 8 < qtiles) {
+            if (qt + kPreThreads / 32 < qtiles) {
 #pragma unroll
-                for (int ks = 0; ks < RT_NF / 4; ++ks) cfrag[ks] = __ldg(Ccat + (int64_t)(q0 + 64 + g) * RT_NF + tig + 4 * ks);
+                for (int ks = 0; ks < RT_NF / 4; ++ks)
+                    cfrag[ks] = __ldg(Ccat + (int64_t)(q0 + kPreThreads / 4 + g) * RT_NF + tig + 4 * ks);
             }
 #pragma unroll
             for (int ks = 0; ks < RT_NF / 4; ++ks) {
@@ -448,23 +473,25 @@ __global__ void __launch_bounds__(256, 1) k_prestep(SweepPlan pl, const double* 
             }
         }
         __syncthreads();
-        // ---- (c) reduced forcing: rows i of From^T, 8 per warp
-        if (mR > 0 && 8 * w < Np) {
-            double acc[4][2];
+        // ---- (c) reduced forcing: warp w takes rows i = 8 (w & 7) .. + 7 of From^T for 16 of the 32 parameters
+        if (mR > 0 && 8 * (w & 7) < Np) {
+            const int it = w & 7, jn0 = 2 * (w >> 3);
+            double acc[2][2];
 #pragma unroll
-            for (int jn = 0; jn < 4; ++jn) acc[jn][0] = acc[jn][1] = 0.0;
-            const double* rcol = Rs + tig * kPreLd + 8 * w + g;
-#pragma unroll 4
+            for (int jn = 0; jn < 2; ++jn) acc[jn][0] = acc[jn][1] = 0.0;
+            const double* rcol = Rs + tig * kPreLd + 8 * it + g;
+            const double* fcol = fs + tig * kPreLdp + 8 * jn0 + g;
+#pragma unroll 8
             for (int ks = 0; ks < mR / 4; ++ks) {
                 const double a = rcol[4 * ks * kPreLd];
 #pragma unroll
-                for (int jn = 0; jn < 4; ++jn) pre_dmma(acc[jn], a, fs[(4 * ks + tig) * kPreLdp + 8 * jn + g]);
+                for (int jn = 0; jn < 2; ++jn) pre_dmma(acc[jn], a, fcol[4 * ks * kPreLdp + 8 * jn]);
             }
-            const int i = 8 * w + g;
+            const int i = 8 * it + g;
             if (i < Np) {
 #pragma unroll
-                for (int jn = 0; jn < 4; ++jn) {
-                    const int64_t p = p0 + 8 * jn + 2 * tig;
+                for (int jn = 0; jn < 2; ++jn) {
+                    const int64_t p = p0 + 8 * (jn0 + jn) + 2 * tig;
                     if (p < pl.Bc) From[p * Np + i] = acc[jn][0];
                     if (p + 1 < pl.Bc) From[(p + 1) * Np + i] = acc[jn][1];
                 }
@@ -1508,7 +1535,7 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
         if (rc) return rc;
         int grid = (pl.Bc + kPreBlock - 1) / kPreBlock;
         if (grid > h->sm_count) grid = h->sm_count;
-        k_prestep<<<grid, 256, kPreSmemBytes, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Ccat,
+        k_prestep<<<grid, kPreThreads, kPreSmemBytes, st>>>(pl, mu_c, t, have_prev, bdf == 2, b.Un, b.Unm1, b.Ccat,
                                                    cx.has_T ? b.Tpad : nullptr, pl.m[kRhs] > 0 ? b.rhs_til : nullptr, dt, b.Wv, b.F,
                                                    b.From);
         RT_LAUNCH_CHECK(h);
