@@ -264,7 +264,8 @@ int64_t rt_sweep_chunk(int64_t B, int N, int sm_count);
 
 /* Per-kernel-class device timing of the online sweep (CUDA events on the caller's stream around every
  * launch of the first parameter chunk).  Classes: 0 state/features, 1 T u* GEMM, 2 sampled entries,
- * 3 theta GEMM, 4 assembly GEMM (K and M), 5 forcing GEMM, 6 LU solve, 7 unused.
+ * 3 theta GEMM, 4 assembly GEMM (K and M), 5 forcing GEMM, 6 LU solve, 7 the fused pre-step kernel (classes 0, 1, 2 and 5
+ * in one launch: N <= 64, trilinear and forcing bases of at most 128 modes).
  * rt_profile_read synchronises, returns accumulated milliseconds and launch counts, and resets. */
 #define RT_PROFILE_CLASSES 8
 int rt_profile_enable(rt_handle* h, int on);

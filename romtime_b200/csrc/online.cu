@@ -1530,7 +1530,7 @@ int sweep_step(rt_handle* h, SweepCtx& cx, const double* mu_c, const double* Fex
     const bool fused = !Fext && mu_c && pl.Npad <= 64 && (!cx.has_T || pl.m[kTril] <= 128) && pl.mpad[kRhs] <= 128 &&
                        pl.Qmat > 0 && !(getenv("RT_FUSED_PRESTEP") && atoi(getenv("RT_FUSED_PRESTEP")) == 0);
     if (fused) {
-        ProfScope ps(prof, pa, 2, st);
+        ProfScope ps(prof, pa, 7, st);
         rc = rt_ensure_smem(h, 11, k_prestep, (int)kPreSmemBytes);
         if (rc) return rc;
         int grid = (pl.Bc + kPreBlock - 1) / kPreBlock;

@@ -585,7 +585,7 @@ def errors_summary(err):
     return out
 
 
-PROFILE_CLASSES = ("state", "gemm_Tu", "entries", "gemm_theta", "gemm_assembly", "gemm_forcing", "lu_solve", "unused")
+PROFILE_CLASSES = ("state", "gemm_Tu", "entries", "gemm_theta", "gemm_assembly", "gemm_forcing", "lu_solve", "prestep_fused")
 
 
 def profile_enable(on=True):

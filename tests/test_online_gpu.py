@@ -255,3 +255,21 @@ def test_step_reuses_staged_model_and_sees_new_tables():
         outs.append(Un.cpu().numpy())
         del dm, Un, Unm1, info
     assert relerr(outs[0], outs[1]) > 1e-3  # different models, different answers
+
+
+@pytest.mark.parametrize("N,m,m_rhs,B", [(64, 128, 128, 300), (40, 24, 7, 95), (64, 16, 16, 33), (33, 128, 40, 64)])
+def test_fused_prestep_matches_the_four_kernel_path(N, m, m_rhs, B, monkeypatch):
+    """k_prestep (state + T u* + sampled entries + forcing in one DMMA kernel) against k_state / k_tu / k_entries / k_forcing:
+    same sweep, the two pre-step paths; ragged last block of 32 parameters, N below 64, bases below 128 modes."""
+    from romtime_b200 import kernels
+
+    model = synthetic.make_piston_model(N=N, m=m, m_rhs=m_rhs, seed=N + m + 7)
+    dm = kernels.DeviceRomModel(model)
+    mus = synthetic.sample_mus(B, seed=5)
+    monkeypatch.setenv("RT_FUSED_PRESTEP", "0")
+    ref, info0 = kernels.online_sweep(dm, mus, 12, 2e-3, bdf=2)
+    monkeypatch.setenv("RT_FUSED_PRESTEP", "1")
+    out, info1 = kernels.online_sweep(dm, mus, 12, 2e-3, bdf=2)
+    assert not info0.any().item() and not info1.any().item()
+    scale = ref.abs().amax(dim=(1, 2), keepdim=True)
+    assert ((out - ref).abs() / scale).max().item() < 1e-11
