@@ -1039,6 +1039,9 @@ __device__ __forceinline__ double gjs_rhs_row(const GjsShared& sh, int i) {
     return s;
 }
 
+// PERSISTENT: a grid smaller than the chunk strides over it (the two-lane experiment of DESIGN.md 8, RT_GJ_GRID); the shipped
+// launch is one system per CTA with no loop and no trailing barrier
+template <bool PERSISTENT>
 __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* __restrict__ Kmat, const double* __restrict__ Mmat,
                                                     const double* __restrict__ Mw,  // M w from the GEMM's matvec hook, or null
                                                     const double* __restrict__ From, const double* __restrict__ Wv, LuExtras ex,
@@ -1050,10 +1053,8 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
     const int g8 = lane >> 2, q = lane & 3;
     const int N = pl.N;
     const bool vec = (N & 1) == 0;
-    // one system per CTA (grid = Bc) or a persistent grid that strides over the chunk (one CTA per SM beside the assembly
-    // GEMM of the other lane, sweep_impl)
 #pragma unroll 1
-    for (int64_t p = blockIdx.x; p < pl.Bc; p += gridDim.x) {
+    for (int64_t p = blockIdx.x; p < (PERSISTENT ? (int64_t)pl.Bc : (int64_t)blockIdx.x + 1); p += gridDim.x) {
     int* info = info_all + p;
     const double* Kp = Kmat + p * pl.ldk;
     const double* Mp = Mmat + p * pl.ldk;
@@ -1174,7 +1175,8 @@ __global__ void __launch_bounds__(128, 6) k_gj_smem(SweepPlan pl, const double* 
             if (uN_out) uN_out[p * out_stride_p + out_off + c] = x;
         }
     }
-    __syncthreads();  // the next system of a persistent CTA re-uses sh
+    if (PERSISTENT) __syncthreads();  // the next system of a persistent CTA re-uses sh
+    else break;
     }
 }
 
@@ -1346,12 +1348,17 @@ inline bool mw_in_gemm(const SweepPlan& pl, const LuExtras& ex) {
 
 int launch_gj(rt_handle* h, const SweepPlan& pl, const SweepBuffers& b, const LuExtras& ex, const StepOut& o, cudaStream_t st) {
 #ifdef RT_GEMM_LAUNCH_REGS
-    RT_CUDA(h, cudaFuncSetAttribute(k_gj_smem, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    RT_CUDA(h, cudaFuncSetAttribute(k_gj_smem<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 #endif
     int gj_grid = pl.Bc;
     if (getenv("RT_GJ_GRID")) { gj_grid = atoi(getenv("RT_GJ_GRID")); if (gj_grid > pl.Bc) gj_grid = pl.Bc; }
-    k_gj_smem<<<gj_grid, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw_in_gemm(pl, ex) ? b.Mw : nullptr, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out,
-                                     o.stride_p, o.off, o.info, o.step);
+    const double* mw = mw_in_gemm(pl, ex) ? b.Mw : nullptr;
+    if (gj_grid < pl.Bc)
+        k_gj_smem<true><<<gj_grid, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
+                                                 o.info, o.step);
+    else
+        k_gj_smem<false><<<pl.Bc, 128, 0, st>>>(pl, b.Kmat, b.Mmat, mw, b.From, b.Wv, ex, b.Un, b.Unm1, o.uN_out, o.stride_p, o.off,
+                                                o.info, o.step);
     RT_LAUNCH_CHECK(h);
     return RT_OK;
 }
